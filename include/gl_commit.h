@@ -1,0 +1,115 @@
+/* gl_commit.h -- C ABI of the B200 STARK-commit library (libglb200.so).
+ *
+ * Drop-in boundary for the commit hot path of MerlinLayer2/merlin-zkevm-prover.  The reference
+ * has no FFI layer; its boundary is the C++ class API called by Starks::genProof
+ * (src/starkpil/starks.cpp:52-56,133-137,214-218,261,284,289) and FRIProve::prove
+ * (src/starkpil/fri/friProve.cpp:100-102,120-123).  Each entry point below names the reference
+ * member it replaces; the header-compatible C++ shims in merlin-zkevm-prover_b200/host/ forward to
+ * these functions.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all matrices are row-major uint64_t words, element (row i,
+ *     column j) of an n x ncols matrix at a[i*ncols + j] (ntt_goldilocks.cpp:95-110).
+ *   - inputs may be any representative in [0, 2^64); every output word is CANONICAL (x mod p,
+ *     p = 2^64 - 2^32 + 1), i.e. equal to Goldilocks::toU64 of the reference's result.
+ *   - every function returns 0 on success, non-zero on error; gl_last_error() describes the last
+ *     failure of the calling thread.  Nothing falls back to the CPU: without a CUDA device the
+ *     calls fail.
+ *   - *_host functions take HOST pointers, are synchronous and include the host<->device copies.
+ *     *_dev functions take DEVICE pointers (cudaMalloc'ed, e.g. from gl_dev_alloc or a torch
+ *     tensor's data_ptr) and run on the library's stream; they are synchronous on return unless
+ *     noted.
+ *   - aliasing follows the reference: dst == src or dst == NULL means in place; extendPol
+ *     allows output == input.  When dst != src the source is not modified.
+ */
+#ifndef GL_COMMIT_H
+#define GL_COMMIT_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GL_OK 0
+#define GL_ERR_CUDA 1
+#define GL_ERR_ARG 2
+#define GL_ERR_RANGE 3 /* domain > 2^32: reference throws std::range_error (ntt_goldilocks.hpp:94-97) */
+#define GL_ERR_NOMEM 4
+#define GL_ERR_NCCL 5
+
+/* ---- lifetime ------------------------------------------------------------------------- */
+/* Bind the calling process to CUDA device `device`, upload constant tables.  Idempotent. */
+int gl_init(int device);
+void gl_shutdown(void);
+const char *gl_last_error(void);
+int gl_device_count(int *count);
+/* Upper bound (bytes) for the library's internal scratch arena; 0 = default (4 GiB). */
+int gl_set_scratch_limit(size_t bytes);
+/* Number of CUDA kernels launched by this library since the last call with reset != 0. */
+uint64_t gl_kernel_launches(int reset);
+
+/* ---- memory helpers ---------------------------------------------------------------------- */
+int gl_dev_alloc(void **dptr, size_t bytes);
+int gl_dev_free(void *dptr);
+int gl_host_alloc(void **hptr, size_t bytes); /* pinned host memory */
+int gl_host_free(void *hptr);
+int gl_h2d(void *dptr, const void *hptr, size_t bytes);
+int gl_d2h(void *hptr, const void *dptr, size_t bytes);
+int gl_sync(void);
+/* cudaStream_t of the library (as void*), for callers that want to order their own work. */
+void *gl_stream(void);
+
+/* ---- device-resident hot path -------------------------------------------------------------- */
+/* NTT_Goldilocks::NTT / INTT (ntt_goldilocks.cpp:166-232, 307-324).
+ * size must be a power of two <= 2^32 (0 or ncols == 0: no-op).  inverse != 0: INTT; extend != 0
+ * (with inverse): coefficient i is additionally multiplied by 7^i (ntt_goldilocks.cpp:124-136). */
+int gl_ntt_dev(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend);
+/* NTT_Goldilocks::extendPol (ntt_goldilocks.cpp:326-352): out[k][c] = P_c(7 * w_E^k), k < n_ext,
+ * where P_c interpolates in[.][c] over the size-n subgroup.  out holds n_ext*ncols words. */
+int gl_extend_pol_dev(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
+/* PoseidonGoldilocks::merkletree_avx / MerkleTreeGL::merkelize (poseidon_goldilocks.cpp:266-301,
+ * merkleTreeGL.cpp:37-44): tree holds (2*nrows-1)*4 words, leaf digests first, root last. */
+int gl_merkletree_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows);
+/* Starks::genProof stage commit (starks.cpp:52-56): extendPol followed by merkelize.
+ * lde (n_ext*ncols words) and tree ((2*n_ext-1)*4 words) are device buffers; root is a HOST
+ * pointer to 4 words. */
+int gl_commit_dev(uint64_t *lde, uint64_t *tree, const uint64_t *in, uint64_t n_ext, uint64_t n,
+                  uint64_t ncols, uint64_t root[4]);
+/* MerkleTreeGL::getGroupProof (merkleTreeGL.cpp:12-35): proof (HOST, width + 4*log2(height) words)
+ * = row idx of src followed by the sibling digests bottom-up; src/tree are device pointers. */
+int gl_group_proof_dev(uint64_t *proof_host, const uint64_t *src, const uint64_t *tree,
+                       uint64_t height, uint64_t width, uint64_t idx);
+/* Batched permutation PoseidonGoldilocks::hash_full_result (poseidon_goldilocks.cpp:166-228):
+ * n states of 12 words. */
+int gl_hash_full_result_dev(uint64_t *out, const uint64_t *in, uint64_t n);
+/* PoseidonGoldilocks::linear_hash of every row (poseidon_goldilocks.cpp:229-265): out = nrows*4 words. */
+int gl_linear_hash_rows_dev(uint64_t *out, const uint64_t *src, uint64_t ncols, uint64_t nrows);
+
+/* ---- host-pointer convenience (what the C++ shims call) -------------------------------------- */
+int gl_ntt_host(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend);
+int gl_extend_pol_host(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
+int gl_merkletree_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows);
+/* extendPol + merkelize with one upload: lde_out / tree_out may be NULL if not wanted. */
+int gl_commit_host(uint64_t *lde_out, uint64_t *tree_out, const uint64_t *in, uint64_t n_ext, uint64_t n,
+                   uint64_t ncols, uint64_t root[4]);
+int gl_hash_full_result_host(uint64_t *out, const uint64_t *in, uint64_t n);
+int gl_linear_hash_host(uint64_t out[4], const uint64_t *in, uint64_t size);
+
+/* Batched field arithmetic, Goldilocks::add/sub/mul (goldilocks_base_field_scalar.hpp:16-160):
+ * op 0 add(a,b), 1 sub(a,b), 2 mul(a,b), 3 a*b+c, 4 add with canonical b, 5 a^2, 6 canonicalise a.
+ * out[i] is canonical.  b / c may be NULL when the op does not use them. */
+int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const uint64_t *c, uint64_t n, int op);
+
+/* ---- layout helpers (merklehash_goldilocks.hpp:25-28, merkleTreeGL.hpp:71-78) ----------------- */
+uint64_t gl_tree_num_elements(uint64_t height);
+uint64_t gl_merkle_proof_size(uint64_t height);
+
+/* ---- per-phase device timings of the last gl_commit_dev / gl_extend_pol_dev / gl_merkletree_dev
+ *      (CUDA events on the library stream), in milliseconds: [0] LDE, [1] leaf hashing, [2] tree levels */
+int gl_last_timings(float ms[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GL_COMMIT_H */

@@ -1,0 +1,213 @@
+// gl64.cuh -- Goldilocks field arithmetic for sm_100a (64-bit integer pipe).
+//
+// p = 2^64 - 2^32 + 1 (reference: src/goldilocks/src/goldilocks_base_field.hpp:14, non-Montgomery).
+// Replaces the reference's scalar x86 asm add/sub/mul (goldilocks_base_field_scalar.hpp:16-160)
+// and the AVX2 mult_avx_128/reduce_avx_128_64 (goldilocks_base_field_avx.hpp:79-358).
+//
+// Representation: one u64 per element.  Like the reference, intermediate values are *lazily
+// reduced*: every routine accepts ANY u64 as a representative and returns some representative
+// in [0, 2^64); gl::canon() produces the canonical value (Goldilocks::toU64,
+// goldilocks_base_field_tools.hpp:152-163).  Everything written to caller-visible memory is
+// canonical.
+//
+// Instruction budget (cuobjdump, sm_100a): mul = 4 IMAD.WIDE + 3 IADD3 (128-bit product) +
+// ~8 for the reduction (2^64 = 2^32-1, 2^96 = -1 mod p) ~ 15 SASS instructions, split about
+// evenly between the FMA pipe (IMAD*) and the ALU pipe (IADD3*), which is what the SM can
+// dual-issue (each pipe takes one warp instruction every other cycle).
+#pragma once
+#include <stdint.h>
+
+namespace gl {
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+constexpr u64 P = 0xFFFFFFFF00000001ULL;
+constexpr u32 EPS = 0xFFFFFFFFu; // 2^64 mod p
+
+struct u128 {
+    u32 x0, x1, x2, x3;
+};
+
+__device__ __forceinline__ u64 pack(u32 lo, u32 hi) { return ((u64)hi << 32) | lo; }
+
+__device__ __forceinline__ u64 canon(u64 x) { return x >= P ? x - P : x; }
+
+// 64x64 -> 128, even/odd column scheme: 4 wide multiplies, one carry chain.
+__device__ __forceinline__ u128 mul_wide(u64 a, u64 b)
+{
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
+    u128 r;
+    asm("{\n\t"
+        ".reg .u64 p, q, y;\n\t"
+        ".reg .u32 p1, q0, q1, y0, y1, c;\n\t"
+        "mul.wide.u32 p, %4, %6;\n\t"
+        "mul.wide.u32 q, %5, %7;\n\t"
+        "mul.wide.u32 y, %4, %7;\n\t"
+        "mov.b64 {%0, p1}, p;\n\t"
+        "mov.b64 {q0, q1}, q;\n\t"
+        "mov.b64 {y0, y1}, y;\n\t"
+        "mad.lo.cc.u32 y0, %5, %6, y0;\n\t"
+        "madc.hi.cc.u32 y1, %5, %6, y1;\n\t"
+        "addc.u32 c, 0, 0;\n\t"
+        "add.cc.u32 %1, p1, y0;\n\t"
+        "addc.cc.u32 %2, q0, y1;\n\t"
+        "addc.u32 %3, q1, c;\n\t"
+        "}"
+        : "=r"(r.x0), "=r"(r.x1), "=r"(r.x2), "=r"(r.x3)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return r;
+}
+
+// a*b + c as a 128-bit value (cannot overflow: (2^64-1)^2 + 2^64-1 < 2^128).
+__device__ __forceinline__ u128 mad_wide(u64 a, u64 b, u64 c)
+{
+    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
+    u32 c0 = (u32)c, c1 = (u32)(c >> 32);
+    u128 r;
+    asm("{\n\t"
+        ".reg .u64 y;\n\t"
+        ".reg .u32 p1, q0, q1, y0, y1, k;\n\t"
+        "mad.lo.cc.u32 %0, %4, %6, %8;\n\t"
+        "madc.hi.cc.u32 p1, %4, %6, %9;\n\t"
+        "madc.lo.cc.u32 q0, %5, %7, 0;\n\t"
+        "madc.hi.u32 q1, %5, %7, 0;\n\t"
+        "mul.wide.u32 y, %4, %7;\n\t"
+        "mov.b64 {y0, y1}, y;\n\t"
+        "mad.lo.cc.u32 y0, %5, %6, y0;\n\t"
+        "madc.hi.cc.u32 y1, %5, %6, y1;\n\t"
+        "addc.u32 k, 0, 0;\n\t"
+        "add.cc.u32 %1, p1, y0;\n\t"
+        "addc.cc.u32 %2, q0, y1;\n\t"
+        "addc.u32 %3, q1, k;\n\t"
+        "}"
+        : "=r"(r.x0), "=r"(r.x1), "=r"(r.x2), "=r"(r.x3)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(c0), "r"(c1));
+    return r;
+}
+
+// x0 + x1 2^32 + x2 2^64 + x3 2^96  ==  {x0,x1} - x3 + x2*(2^32-1)   (mod p)
+// One net correction k = carry - borrow in {-1,0,1}; result in [0, 2^64), not nec. canonical.
+// Valid for ANY 128-bit input.
+__device__ __forceinline__ u64 reduce128(u128 x)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 b, k, kl, kh;\n\t"
+        "sub.cc.u32 %0, %2, %5;\n\t"
+        "subc.cc.u32 %1, %3, 0;\n\t"
+        "subc.u32 b, 0, 0;\n\t"                      // b = -borrow
+        "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %0;\n\t"
+        "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %1;\n\t"
+        "addc.u32 k, b, 0;\n\t"                      // k = carry - borrow
+        "neg.s32 kl, k;\n\t"
+        "shr.s32 kh, k, 31;\n\t"
+        "add.cc.u32 %0, %0, kl;\n\t"                 // r += k*(2^32-1)
+        "addc.u32 %1, %1, kh;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(x.x0), "r"(x.x1), "r"(x.x2), "r"(x.x3));
+    return pack(r0, r1);
+}
+
+// 96-bit input (x3 == 0): {x0,x1} + x2*(2^32-1); one carry correction.
+__device__ __forceinline__ u64 reduce96(u32 x0, u32 x1, u32 x2)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 k;\n\t"
+        "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %2;\n\t"
+        "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %3;\n\t"
+        "addc.u32 k, 0, 0;\n\t"
+        "neg.s32 k, k;\n\t"                          // 0 or 0xFFFFFFFF
+        "add.cc.u32 %0, %0, k;\n\t"
+        "addc.u32 %1, %1, 0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(x0), "r"(x1), "r"(x2));
+    return pack(r0, r1);
+}
+
+__device__ __forceinline__ u64 mul(u64 a, u64 b) { return reduce128(mul_wide(a, b)); }
+__device__ __forceinline__ u64 sqr(u64 a) { return reduce128(mul_wide(a, a)); }
+// a*b + c  (fused: the addend rides on the first partial product)
+__device__ __forceinline__ u64 mad(u64 a, u64 b, u64 c) { return reduce128(mad_wide(a, b, c)); }
+
+// a + b for arbitrary representatives.  Two possible wraps (reference add: scalar.hpp:16-35).
+__device__ __forceinline__ u64 add(u64 a, u64 b)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 k;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\t"
+        "addc.cc.u32 %1, %3, %5;\n\t"
+        "addc.u32 k, 0, 0;\n\t"
+        "neg.s32 k, k;\n\t"
+        "add.cc.u32 %0, %0, k;\n\t"
+        "addc.cc.u32 %1, %1, 0;\n\t"
+        "addc.u32 k, 0, 0;\n\t"
+        "neg.s32 k, k;\n\t"
+        "add.cc.u32 %0, %0, k;\n\t"
+        "addc.u32 %1, %1, 0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    return pack(r0, r1);
+}
+
+// a + b where b is CANONICAL (< p): a single wrap suffices.
+__device__ __forceinline__ u64 add_c(u64 a, u64 b)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 k;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\t"
+        "addc.cc.u32 %1, %3, %5;\n\t"
+        "addc.u32 k, 0, 0;\n\t"
+        "neg.s32 k, k;\n\t"
+        "add.cc.u32 %0, %0, k;\n\t"
+        "addc.u32 %1, %1, 0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    return pack(r0, r1);
+}
+
+// a - b where b is CANONICAL (< p): a single wrap suffices.
+__device__ __forceinline__ u64 sub_c(u64 a, u64 b)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 k;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\t"
+        "subc.cc.u32 %1, %3, %5;\n\t"
+        "subc.u32 k, 0, 0;\n\t"                      // 0 or 0xFFFFFFFF
+        "sub.cc.u32 %0, %0, k;\n\t"                  // r -= (2^32-1) on borrow
+        "subc.u32 %1, %1, 0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    return pack(r0, r1);
+}
+
+// a - b for arbitrary representatives.
+__device__ __forceinline__ u64 sub(u64 a, u64 b) { return sub_c(a, canon(b)); }
+
+__device__ __forceinline__ u64 neg(u64 a)
+{
+    a = canon(a);
+    return a ? P - a : 0;
+}
+
+__device__ __forceinline__ u64 pow(u64 a, u64 e)
+{
+    u64 r = 1;
+    while (e) {
+        if (e & 1) r = mul(r, a);
+        a = sqr(a);
+        e >>= 1;
+    }
+    return r;
+}
+
+} // namespace gl

@@ -1,0 +1,624 @@
+// glb200.cu -- C ABI (include/gl_commit.h) over the sm_100a kernels.
+//
+// One process drives one GPU.  The library owns a stream, a grow-only scratch arena and the
+// constant tables; all kernels are launched here.  There is NO CPU fallback: every compute entry
+// point fails with GL_ERR_CUDA when no device is usable.
+#include "../../include/gl_commit.h"
+#include "ntt.cuh"
+#include "poseidon_kernels.cuh"
+
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace {
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+typedef unsigned __int128 u128_t;
+
+thread_local std::string t_err;
+
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    t_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(e__ == cudaErrorMemoryAllocation ? GL_ERR_NOMEM : GL_ERR_CUDA, "%s: %s (%s:%d)", #call, \
+                        cudaGetErrorString(e__), __FILE__, __LINE__);                              \
+    } while (0)
+
+#define TRY(call)                   \
+    do {                            \
+        int rc__ = (call);          \
+        if (rc__ != GL_OK) return rc__; \
+    } while (0)
+
+struct Ctx {
+    bool ready = false;
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    void *arena = nullptr;
+    size_t arena_bytes = 0;
+    size_t scratch_limit = (size_t)8 << 30;
+    std::atomic<uint64_t> launches{0};
+    float ms[3] = {0, 0, 0};
+    std::mutex mu;
+} g;
+
+// ---- host-side field helpers (table generation only) -------------------------------------------
+const u64 P = 0xFFFFFFFF00000001ULL;
+u64 hmul(u64 a, u64 b) { return (u64)(((u128_t)a * b) % P); }
+u64 hpow(u64 a, u64 e)
+{
+    u64 r = 1;
+    while (e) {
+        if (e & 1) r = hmul(r, a);
+        a = hmul(a, a);
+        e >>= 1;
+    }
+    return r;
+}
+const u64 W32 = 7277203076849721926ULL; // Goldilocks::W[32], goldilocks_base_field.cpp:44
+
+int upload_tables()
+{
+    static u64 w32[4][256], p7[4][256], inv2[33], w256[2][256];
+    for (int j = 0; j < 4; j++) {
+        u64 gw = hpow(W32, 1ULL << (8 * j)), g7 = hpow(7, 1ULL << (8 * j));
+        w32[j][0] = p7[j][0] = 1;
+        for (int i = 1; i < 256; i++) {
+            w32[j][i] = hmul(w32[j][i - 1], gw);
+            p7[j][i] = hmul(p7[j][i - 1], g7);
+        }
+    }
+    u64 half = hpow(2, P - 2);
+    inv2[0] = 1;
+    for (int i = 1; i <= 32; i++) inv2[i] = hmul(inv2[i - 1], half);
+    u64 w = hpow(W32, 1ULL << 24), wi = hpow(w, P - 2);
+    if (hpow(w, 16) != 4096 || hpow(w, 4) != 8) return fail(GL_ERR_ARG, "root-of-unity chain mismatch");
+    w256[0][0] = w256[1][0] = 1;
+    for (int i = 1; i < 256; i++) {
+        w256[0][i] = hmul(w256[0][i - 1], w);
+        w256[1][i] = hmul(w256[1][i - 1], wi);
+    }
+    CU(cudaMemcpyToSymbol(ntt::c_w32, w32, sizeof w32));
+    CU(cudaMemcpyToSymbol(ntt::c_p7, p7, sizeof p7));
+    CU(cudaMemcpyToSymbol(ntt::c_inv2, inv2, sizeof inv2));
+    CU(cudaMemcpyToSymbol(ntt::c_w256, w256, sizeof w256));
+    CU(poseidon::upload_constants());
+    return GL_OK;
+}
+
+int need_ctx()
+{
+    if (!g.ready) return gl_init(0);
+    return GL_OK;
+}
+
+int arena_reserve(size_t bytes)
+{
+    if (bytes <= g.arena_bytes) return GL_OK;
+    if (g.arena) {
+        CU(cudaStreamSynchronize(g.stream));
+        CU(cudaFree(g.arena));
+        g.arena = nullptr;
+        g.arena_bytes = 0;
+    }
+    CU(cudaMalloc(&g.arena, bytes));
+    g.arena_bytes = bytes;
+    return GL_OK;
+}
+
+u32 ilog2(u64 n)
+{
+    u32 k = 0;
+    while ((1ULL << k) < n) k++;
+    return k;
+}
+
+bool is_pow2(u64 n) { return n && !(n & (n - 1)); }
+
+// ---- NTT plan / launch ---------------------------------------------------------------------------
+template <int B2, bool INV>
+int launch_pass_t(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
+{
+    constexpr int R = 16 << B2;
+    size_t smem = (B2 > 0 ? (size_t)R * ntt::kTileCols * 8 : 0) + (size_t)R * 8 + 32 * 8;
+    static bool attr_done = false;
+    if (!attr_done) {
+        CU(cudaFuncSetAttribute(ntt::k_pass<B2, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done = true;
+    }
+    dim3 grid((unsigned)ntiles, coltiles), block(32, 1 << B2);
+    ntt::k_pass<B2, INV><<<grid, block, smem, g.stream>>>(p);
+    g.launches++;
+    CU(cudaGetLastError());
+    return GL_OK;
+}
+
+int launch_pass(const ntt::PassParams &p)
+{
+    u32 b = p.bits[p.pass];
+    u64 ntiles = (1ULL << p.logn) >> b;
+    u32 coltiles = (p.ncols + ntt::kTileCols - 1) / ntt::kTileCols;
+    if (ntiles > 0x7FFFFFFFULL || coltiles > 65535) return fail(GL_ERR_ARG, "grid too large");
+    switch ((b - 4) * 2 + (p.inverse ? 1 : 0)) {
+    case 0: return launch_pass_t<0, false>(p, ntiles, coltiles);
+    case 1: return launch_pass_t<0, true>(p, ntiles, coltiles);
+    case 2: return launch_pass_t<1, false>(p, ntiles, coltiles);
+    case 3: return launch_pass_t<1, true>(p, ntiles, coltiles);
+    case 4: return launch_pass_t<2, false>(p, ntiles, coltiles);
+    case 5: return launch_pass_t<2, true>(p, ntiles, coltiles);
+    case 6: return launch_pass_t<3, false>(p, ntiles, coltiles);
+    case 7: return launch_pass_t<3, true>(p, ntiles, coltiles);
+    case 8: return launch_pass_t<4, false>(p, ntiles, coltiles);
+    case 9: return launch_pass_t<4, true>(p, ntiles, coltiles);
+    }
+    return fail(GL_ERR_ARG, "bad pass width %u", b);
+}
+
+// One transform of `ncols` columns (ncols small enough for tmp).  src/dst may alias.
+// scale_mode: 0 none, 1: 1/n, 2: 7^i/n.  nvalid: rows >= nvalid of src are zeros.
+int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpitch, u32 logn, u32 ncols,
+            bool inverse, int scale_mode, u64 nvalid)
+{
+    ntt::PassParams p;
+    memset(&p, 0, sizeof p);
+    p.ncols = ncols;
+    p.logn = logn;
+    p.inverse = inverse ? 1 : 0;
+    if (logn <= 3) {
+        p.src = src; p.dst = dst; p.spitch = spitch; p.dpitch = dpitch;
+        p.scale_mode = scale_mode; p.nvalid = nvalid; p.npass = 1;
+        ntt::k_tiny<<<(ncols + 127) / 128, 128, 0, g.stream>>>(p);
+        g.launches++;
+        CU(cudaGetLastError());
+        return GL_OK;
+    }
+    u32 m = (logn + 7) / 8;
+    p.npass = m;
+    for (u32 i = 0; i < m; i++) p.bits[i] = logn / m + (i < logn % m ? 1 : 0);
+    u32 prev = 0;
+    for (u32 i = 0; i < m; i++) {
+        p.pass = i;
+        p.log_prev = prev;
+        p.log_rest = logn - prev - p.bits[i];
+        bool first = (i == 0), last = (i + 1 == m);
+        p.src = first ? src : tmp;
+        p.spitch = first ? spitch : tpitch;
+        p.dst = last ? dst : tmp;
+        p.dpitch = last ? dpitch : tpitch;
+        p.nvalid = first ? nvalid : (1ULL << logn);
+        p.scale_mode = last ? scale_mode : 0;
+        TRY(launch_pass(p));
+        prev += p.bits[i];
+    }
+    return GL_OK;
+}
+
+u32 pick_col_block(u64 ncols, size_t bytes_per_col)
+{
+    u64 cb = g.scratch_limit / bytes_per_col;
+    cb = (cb / 32) * 32;
+    if (cb < 32) cb = 32;
+    if (cb > ncols) cb = ncols;
+    return (u32)cb;
+}
+
+int ntt_dev(u64 *dst, const u64 *src, u64 size, u64 ncols, int inverse, int extend)
+{
+    if (size == 0 || ncols == 0) return GL_OK; // ntt_goldilocks.cpp:168-171
+    if (!is_pow2(size)) return fail(GL_ERR_ARG, "NTT size %llu is not a power of two", size);
+    if (size > (1ULL << 32)) return fail(GL_ERR_RANGE, "Domain size too big for the curve");
+    if (!dst) dst = (u64 *)src;
+    u32 logn = ilog2(size);
+    int mode = inverse ? (extend ? 2 : 1) : 0;
+    u32 cb = pick_col_block(ncols, size * 8);
+    if (logn > 8) TRY(arena_reserve((size_t)size * cb * 8));
+    for (u64 c0 = 0; c0 < ncols; c0 += cb) {
+        u32 w = (u32)((ncols - c0 < cb) ? ncols - c0 : cb);
+        TRY(run_ntt(dst + c0, ncols, src + c0, ncols, (u64 *)g.arena, cb, logn, w, inverse != 0, mode, size));
+    }
+    return GL_OK;
+}
+
+int extend_pol_dev(u64 *out, const u64 *in, u64 n_ext, u64 n, u64 ncols)
+{
+    if (n == 0 || ncols == 0) return GL_OK;
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "extendPol: bad sizes %llu -> %llu", n, n_ext);
+    if (n_ext > (1ULL << 32)) return fail(GL_ERR_RANGE, "Domain size too big for the curve");
+    u32 logn = ilog2(n), loge = ilog2(n_ext);
+    u32 cb = pick_col_block(ncols, (n + n_ext) * 8);
+    TRY(arena_reserve((size_t)(n + n_ext) * cb * 8));
+    u64 *coef = (u64 *)g.arena;          // n x cb      INTT result, scaled by 7^i / n
+    u64 *tmp = coef + (size_t)n * cb;    // n_ext x cb  pass scratch
+    for (u64 c0 = 0; c0 < ncols; c0 += cb) {
+        u32 w = (u32)((ncols - c0 < cb) ? ncols - c0 : cb);
+        TRY(run_ntt(coef, cb, in + c0, ncols, tmp, cb, logn, w, true, 2, n));
+        TRY(run_ntt(out + c0, ncols, coef, cb, tmp, cb, loge, w, false, 0, n));
+    }
+    return GL_OK;
+}
+
+int merkletree_dev(u64 *tree, const u64 *src, u64 ncols, u64 nrows, bool timed)
+{
+    if (nrows == 0) return GL_OK; // poseidon_goldilocks.cpp:268-271
+    if (timed) CU(cudaEventRecord(g.ev[1], g.stream));
+    poseidon::launch_linear_hash_rows(tree, src, nrows, ncols, ncols, g.stream);
+    g.launches++;
+    CU(cudaGetLastError());
+    if (timed) CU(cudaEventRecord(g.ev[2], g.stream));
+    g.launches += poseidon::launch_tree_levels(tree, nrows, g.stream);
+    CU(cudaGetLastError());
+    if (timed) CU(cudaEventRecord(g.ev[3], g.stream));
+    return GL_OK;
+}
+
+int collect_timings(bool lde, bool tree)
+{
+    CU(cudaStreamSynchronize(g.stream));
+    if (lde) CU(cudaEventElapsedTime(&g.ms[0], g.ev[0], g.ev[1])); else g.ms[0] = 0;
+    if (tree) {
+        CU(cudaEventElapsedTime(&g.ms[1], g.ev[1], g.ev[2]));
+        CU(cudaEventElapsedTime(&g.ms[2], g.ev[2], g.ev[3]));
+    } else {
+        g.ms[1] = g.ms[2] = 0;
+    }
+    return GL_OK;
+}
+
+__global__ void k_gather_proof(u64 *proof, const u64 *src, const u64 *tree, u64 height, u64 width, u64 idx)
+{
+    u64 tid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid < width) {
+        proof[tid] = gl::canon(src[idx * width + tid]);
+        return;
+    }
+    u64 k = tid - width; // sibling word k: level k/4, word k%4   (merkleTreeGL.cpp:24-35)
+    u64 level = k >> 2, off = 0, n = height;
+    for (u64 l = 0; l < level; l++) {
+        off += n * 4;
+        n >>= 1;
+    }
+    if (n <= 1) return;
+    u64 sib = (idx >> level) ^ 1;
+    proof[tid] = gl::canon(tree[off + sib * 4 + (k & 3)]);
+}
+
+// Batched Goldilocks::add/sub/mul (goldilocks_base_field_scalar.hpp:16-160) -- F1 parity entry point.
+__global__ void k_field_op(u64 *out, const u64 *a, const u64 *b, const u64 *c, u64 n, int op)
+{
+    u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    u64 r;
+    switch (op) {
+    case 0: r = gl::add(a[i], b[i]); break;
+    case 1: r = gl::sub(a[i], b[i]); break;
+    case 2: r = gl::mul(a[i], b[i]); break;
+    case 3: r = gl::mad(a[i], b[i], c[i]); break;
+    case 4: r = gl::add_c(a[i], gl::canon(b[i])); break;
+    case 5: r = gl::sqr(a[i]); break;
+    default: r = a[i];
+    }
+    out[i] = gl::canon(r);
+}
+
+struct DevBuf {
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes)
+    {
+        CU(cudaMalloc(&p, bytes ? bytes : 8));
+        return GL_OK;
+    }
+    uint64_t *w() { return (uint64_t *)p; }
+};
+
+} // namespace
+
+// =================================================================================================
+extern "C" {
+
+const char *gl_last_error(void) { return t_err.c_str(); }
+
+int gl_device_count(int *count)
+{
+    CU(cudaGetDeviceCount(count));
+    return GL_OK;
+}
+
+int gl_init(int device)
+{
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (g.ready && g.device == device) return GL_OK;
+    if (g.ready) return fail(GL_ERR_ARG, "already bound to device %d", g.device);
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(GL_ERR_CUDA, "no CUDA device %d (found %d)", device, n);
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(GL_ERR_CUDA, "device %s is sm_%d%d; this library is built for sm_100a only", prop.name, prop.major, prop.minor);
+    CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    for (auto &e : g.ev) CU(cudaEventCreate(&e));
+    TRY(upload_tables());
+    g.device = device;
+    g.ready = true;
+    return GL_OK;
+}
+
+void gl_shutdown(void)
+{
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.ready) return;
+    cudaStreamSynchronize(g.stream);
+    if (g.arena) cudaFree(g.arena);
+    g.arena = nullptr;
+    g.arena_bytes = 0;
+    for (auto &e : g.ev) { cudaEventDestroy(e); e = nullptr; }
+    cudaStreamDestroy(g.stream);
+    g.stream = nullptr;
+    g.ready = false;
+    g.device = -1;
+}
+
+int gl_set_scratch_limit(size_t bytes)
+{
+    g.scratch_limit = bytes ? bytes : ((size_t)8 << 30);
+    return GL_OK;
+}
+
+uint64_t gl_kernel_launches(int reset)
+{
+    uint64_t v = g.launches.load();
+    if (reset) g.launches = 0;
+    return v;
+}
+
+int gl_dev_alloc(void **dptr, size_t bytes)
+{
+    TRY(need_ctx());
+    CU(cudaMalloc(dptr, bytes ? bytes : 8));
+    return GL_OK;
+}
+int gl_dev_free(void *dptr)
+{
+    if (dptr) CU(cudaFree(dptr));
+    return GL_OK;
+}
+int gl_host_alloc(void **hptr, size_t bytes)
+{
+    TRY(need_ctx());
+    CU(cudaHostAlloc(hptr, bytes ? bytes : 8, cudaHostAllocDefault));
+    return GL_OK;
+}
+int gl_host_free(void *hptr)
+{
+    if (hptr) CU(cudaFreeHost(hptr));
+    return GL_OK;
+}
+int gl_h2d(void *dptr, const void *hptr, size_t bytes)
+{
+    TRY(need_ctx());
+    CU(cudaMemcpyAsync(dptr, hptr, bytes, cudaMemcpyHostToDevice, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+int gl_d2h(void *hptr, const void *dptr, size_t bytes)
+{
+    TRY(need_ctx());
+    CU(cudaMemcpyAsync(hptr, dptr, bytes, cudaMemcpyDeviceToHost, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+int gl_sync(void)
+{
+    TRY(need_ctx());
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+void *gl_stream(void) { return (void *)g.stream; }
+
+uint64_t gl_tree_num_elements(uint64_t height) { return height ? height * 4 + (height - 1) * 4 : 0; }
+
+uint64_t gl_merkle_proof_size(uint64_t height)
+{
+    if (height > 1) return (uint64_t)ceil(log10((double)height) / log10(2.0)); // merkleTreeGL.hpp:71-78
+    return 0;
+}
+
+int gl_last_timings(float ms[3])
+{
+    ms[0] = g.ms[0]; ms[1] = g.ms[1]; ms[2] = g.ms[2];
+    return GL_OK;
+}
+
+// ---- device-resident ----------------------------------------------------------------------------
+int gl_ntt_dev(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend)
+{
+    TRY(need_ctx());
+    CU(cudaEventRecord(g.ev[0], g.stream));
+    TRY(ntt_dev((u64 *)dst, (const u64 *)src, size, ncols, inverse, extend));
+    CU(cudaEventRecord(g.ev[1], g.stream));
+    return collect_timings(true, false);
+}
+
+int gl_extend_pol_dev(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols)
+{
+    TRY(need_ctx());
+    CU(cudaEventRecord(g.ev[0], g.stream));
+    TRY(extend_pol_dev((u64 *)out, (const u64 *)in, n_ext, n, ncols));
+    CU(cudaEventRecord(g.ev[1], g.stream));
+    return collect_timings(true, false);
+}
+
+int gl_merkletree_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows)
+{
+    TRY(need_ctx());
+    if (nrows == 0) return GL_OK;
+    TRY(merkletree_dev((u64 *)tree, (const u64 *)src, ncols, nrows, true));
+    return collect_timings(false, true);
+}
+
+int gl_commit_dev(uint64_t *lde, uint64_t *tree, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols,
+                  uint64_t root[4])
+{
+    TRY(need_ctx());
+    if (n == 0 || n_ext == 0) return fail(GL_ERR_ARG, "commit: empty domain");
+    CU(cudaEventRecord(g.ev[0], g.stream));
+    TRY(extend_pol_dev((u64 *)lde, (const u64 *)in, n_ext, n, ncols));
+    TRY(merkletree_dev((u64 *)tree, (const u64 *)lde, ncols, n_ext, true));
+    if (root)
+        CU(cudaMemcpyAsync(root, tree + gl_tree_num_elements(n_ext) - 4, 32, cudaMemcpyDeviceToHost, g.stream));
+    return collect_timings(true, true);
+}
+
+int gl_group_proof_dev(uint64_t *proof_host, const uint64_t *src, const uint64_t *tree, uint64_t height,
+                       uint64_t width, uint64_t idx)
+{
+    TRY(need_ctx());
+    if (height == 0 || idx >= height) return fail(GL_ERR_ARG, "getGroupProof: idx %llu out of range", (u64)idx);
+    u64 levels = 0;
+    while ((height >> levels) > 1) levels++;
+    u64 words = width + 4 * levels;
+    if (words == 0) return GL_OK;
+    DevBuf d;
+    TRY(d.alloc(words * 8));
+    k_gather_proof<<<(unsigned)((words + 127) / 128), 128, 0, g.stream>>>((u64 *)d.p, (const u64 *)src, (const u64 *)tree,
+                                                                          height, width, idx);
+    g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(proof_host, d.p, words * 8, cudaMemcpyDeviceToHost, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_hash_full_result_dev(uint64_t *out, const uint64_t *in, uint64_t n)
+{
+    TRY(need_ctx());
+    poseidon::launch_hash_full_result((u64 *)out, (const u64 *)in, n, g.stream);
+    if (n) g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_linear_hash_rows_dev(uint64_t *out, const uint64_t *src, uint64_t ncols, uint64_t nrows)
+{
+    TRY(need_ctx());
+    poseidon::launch_linear_hash_rows((u64 *)out, (const u64 *)src, nrows, ncols, ncols, g.stream);
+    if (nrows) g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+// ---- host-pointer convenience --------------------------------------------------------------------
+int gl_ntt_host(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend)
+{
+    if (size == 0 || ncols == 0) return GL_OK;
+    TRY(need_ctx());
+    if (!dst) dst = (uint64_t *)src;
+    size_t bytes = (size_t)size * ncols * 8;
+    DevBuf d;
+    TRY(d.alloc(bytes));
+    TRY(gl_h2d(d.p, src, bytes));
+    TRY(gl_ntt_dev(d.w(), d.w(), size, ncols, inverse, extend));
+    return gl_d2h(dst, d.p, bytes);
+}
+
+int gl_extend_pol_host(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols)
+{
+    if (n == 0 || ncols == 0) return GL_OK;
+    TRY(need_ctx());
+    DevBuf d;
+    TRY(d.alloc((size_t)n_ext * ncols * 8));
+    TRY(gl_h2d(d.p, in, (size_t)n * ncols * 8));
+    TRY(gl_extend_pol_dev(d.w(), d.w(), n_ext, n, ncols));
+    return gl_d2h(out, d.p, (size_t)n_ext * ncols * 8);
+}
+
+int gl_merkletree_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows)
+{
+    if (nrows == 0) return GL_OK;
+    TRY(need_ctx());
+    DevBuf s, t;
+    TRY(s.alloc((size_t)nrows * ncols * 8));
+    TRY(t.alloc(gl_tree_num_elements(nrows) * 8));
+    if (ncols) TRY(gl_h2d(s.p, src, (size_t)nrows * ncols * 8));
+    TRY(gl_merkletree_dev(t.w(), s.w(), ncols, nrows));
+    return gl_d2h(tree, t.p, gl_tree_num_elements(nrows) * 8);
+}
+
+int gl_commit_host(uint64_t *lde_out, uint64_t *tree_out, const uint64_t *in, uint64_t n_ext, uint64_t n,
+                   uint64_t ncols, uint64_t root[4])
+{
+    TRY(need_ctx());
+    if (n == 0 || n_ext == 0) return fail(GL_ERR_ARG, "commit: empty domain");
+    DevBuf l, t;
+    TRY(l.alloc((size_t)n_ext * ncols * 8));
+    TRY(t.alloc(gl_tree_num_elements(n_ext) * 8));
+    if (ncols) TRY(gl_h2d(l.p, in, (size_t)n * ncols * 8));
+    TRY(gl_commit_dev(l.w(), t.w(), l.w(), n_ext, n, ncols, root));
+    if (lde_out && ncols) TRY(gl_d2h(lde_out, l.p, (size_t)n_ext * ncols * 8));
+    if (tree_out) TRY(gl_d2h(tree_out, t.p, gl_tree_num_elements(n_ext) * 8));
+    return GL_OK;
+}
+
+int gl_hash_full_result_host(uint64_t *out, const uint64_t *in, uint64_t n)
+{
+    if (n == 0) return GL_OK;
+    TRY(need_ctx());
+    DevBuf d;
+    TRY(d.alloc((size_t)n * 96));
+    TRY(gl_h2d(d.p, in, (size_t)n * 96));
+    TRY(gl_hash_full_result_dev(d.w(), d.w(), n));
+    return gl_d2h(out, d.p, (size_t)n * 96);
+}
+
+int gl_linear_hash_host(uint64_t out[4], const uint64_t *in, uint64_t size)
+{
+    TRY(need_ctx());
+    DevBuf s, o;
+    TRY(s.alloc((size_t)size * 8));
+    TRY(o.alloc(32));
+    if (size) TRY(gl_h2d(s.p, in, (size_t)size * 8));
+    TRY(gl_linear_hash_rows_dev(o.w(), s.w(), size, 1));
+    return gl_d2h(out, o.p, 32);
+}
+
+int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const uint64_t *c, uint64_t n, int op)
+{
+    if (n == 0) return GL_OK;
+    TRY(need_ctx());
+    if (op < 0 || op > 6) return fail(GL_ERR_ARG, "unknown field op %d", op);
+    DevBuf d;
+    TRY(d.alloc((size_t)n * 8 * 4));
+    u64 *base = (u64 *)d.p;
+    TRY(gl_h2d(base, a, n * 8));
+    TRY(gl_h2d(base + n, b ? b : a, n * 8));
+    TRY(gl_h2d(base + 2 * n, c ? c : a, n * 8));
+    k_field_op<<<(unsigned)((n + 255) / 256), 256, 0, g.stream>>>(base + 3 * n, base, base + n, base + 2 * n, n, op);
+    g.launches++;
+    CU(cudaGetLastError());
+    return gl_d2h(out, base + 3 * n, n * 8);
+}
+
+} // extern "C"

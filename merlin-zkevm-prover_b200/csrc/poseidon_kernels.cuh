@@ -1,0 +1,118 @@
+// poseidon_kernels.cuh -- leaf (row sponge) and tree-level kernels + launchers.
+//
+//   k_linear_hash_rows : PoseidonGoldilocks::linear_hash over every row   (poseidon_goldilocks.cpp:229-265, loop :277-281)
+//   k_tree_level       : parent = hash(left || right || 0,0,0,0)[0..4)     (poseidon_goldilocks.cpp:287-300)
+//   k_hash_full_result : batched permutation (KAT entry point)             (poseidon_goldilocks.cpp:166-228)
+#pragma once
+#include "poseidon.cuh"
+#include <cuda_runtime.h>
+
+namespace poseidon {
+
+constexpr int kThreads = 128;
+
+__global__ void __launch_bounds__(kThreads) k_hash_full_result(u64 *__restrict__ out, const u64 *__restrict__ in, u64 n)
+{
+    u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n) return;
+    u64 s[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) s[i] = in[idx * 12 + i];
+    permute(s);
+#pragma unroll
+    for (int i = 0; i < 12; i++) out[idx * 12 + i] = gl::canon(s[i]);
+}
+
+// One thread per row.  Row r starts at src + r*pitch and has ncols words (pitch in words).
+// ncols <= 4: the row is returned zero-padded WITHOUT hashing (reference :234-239).
+__global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__ digests, const u64 *__restrict__ src,
+                                                               u64 nrows, u64 ncols, u64 pitch)
+{
+    u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    const u64 *p = src + row * pitch;
+    u64 *d = digests + row * 4;
+    if (ncols <= 4) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) d[i] = (u64)i < ncols ? gl::canon(p[i]) : 0;
+        return;
+    }
+    u64 s[12];
+#pragma unroll
+    for (int i = 8; i < 12; i++) s[i] = 0;
+    u64 full = ncols >> 3;
+    for (u64 c = 0; c < full; c++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) s[i] = p[c * 8 + i];
+        permute(s);
+#pragma unroll
+        for (int i = 0; i < 4; i++) s[8 + i] = s[i];
+    }
+    u32 rem = (u32)(ncols & 7);
+    if (rem) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) s[i] = (u32)i < rem ? p[full * 8 + i] : 0;
+        permute(s);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) d[i] = gl::canon(s[i]);
+}
+
+__global__ void __launch_bounds__(kThreads) k_tree_level(u64 *__restrict__ parents, const u64 *__restrict__ children, u64 nparents)
+{
+    u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= nparents) return;
+    u64 s[12];
+    const ulonglong2 *c = reinterpret_cast<const ulonglong2 *>(children + idx * 8);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        ulonglong2 v = c[i];
+        s[2 * i] = v.x;
+        s[2 * i + 1] = v.y;
+    }
+#pragma unroll
+    for (int i = 8; i < 12; i++) s[i] = 0;
+    permute(s);
+    ulonglong2 *o = reinterpret_cast<ulonglong2 *>(parents + idx * 4);
+    o[0] = make_ulonglong2(gl::canon(s[0]), gl::canon(s[1]));
+    o[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
+}
+
+inline cudaError_t upload_constants()
+{
+    cudaError_t e;
+    if ((e = cudaMemcpyToSymbol(c_RC, GLP_RC, sizeof(GLP_RC))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_PM, GLP_PM, sizeof(GLP_PM))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_SP, GLP_SP, sizeof(GLP_SP))) != cudaSuccess) return e;
+    return cudaSuccess;
+}
+
+inline unsigned grid_for(u64 n) { return (unsigned)((n + kThreads - 1) / kThreads); }
+
+inline void launch_hash_full_result(u64 *out, const u64 *in, u64 n, cudaStream_t st)
+{
+    if (n) k_hash_full_result<<<grid_for(n), kThreads, 0, st>>>(out, in, n);
+}
+
+inline void launch_linear_hash_rows(u64 *digests, const u64 *src, u64 nrows, u64 ncols, u64 pitch, cudaStream_t st)
+{
+    if (nrows) k_linear_hash_rows<<<grid_for(nrows), kThreads, 0, st>>>(digests, src, nrows, ncols, pitch);
+}
+
+// Levels above the leaves.  tree holds (2*nrows-1)*4 words, leaves first (merklehash_goldilocks.hpp:25-28).
+// Returns the number of kernels launched.
+inline int launch_tree_levels(u64 *tree, u64 nrows, cudaStream_t st)
+{
+    int launches = 0;
+    u64 pending = nrows, next_index = 0;
+    while (pending > 1) {
+        u64 next_n = (pending - 1) / 2 + 1; // reference :283-300 (power-of-two heights only are meaningful)
+        k_tree_level<<<grid_for(next_n), kThreads, 0, st>>>(tree + next_index + pending * 4, tree + next_index, next_n);
+        launches++;
+        next_index += pending * 4;
+        pending /= 2;
+    }
+    return launches;
+}
+
+} // namespace poseidon

@@ -1,0 +1,251 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libglb200.so), against the reference's
+golden vectors, the stored reference outputs and the CPU oracle on identical seeded inputs.
+Bar: bit-exact on canonical values for every LDE word, every Merkle node and the root."""
+import numpy as np
+import pytest
+
+from conftest import P, fib_rows, fib_vec, hexs
+
+pytestmark = pytest.mark.gpu
+
+EDGE = [0, 1, 2, 2**32 - 2, 2**32 - 1, 2**32, 2**32 + 1, P - 2, P - 1, P, P + 1, 2**63, 2**64 - 2**32, 2**64 - 2, 2**64 - 1,
+        0xFFFFFFFE00000001, 0xFFFFFFFF00000000, 0x00000001FFFFFFFF]
+
+
+def _pairs(rng, n):
+    e = np.array(EDGE, dtype=np.uint64)
+    a = np.concatenate([np.repeat(e, len(e)), rng.integers(0, 2**64 - 1, size=n, dtype=np.uint64, endpoint=True)])
+    b = np.concatenate([np.tile(e, len(e)), rng.integers(0, 2**64 - 1, size=n, dtype=np.uint64, endpoint=True)])
+    return a, b
+
+
+def test_field_ops(glb):
+    """F1: add/sub/mul on arbitrary (also non-canonical) representatives vs exact integer arithmetic."""
+    rng = np.random.default_rng(1)
+    a, b = _pairs(rng, 20000)
+    c = np.roll(a, 7)
+    ai, bi, ci = [int(x) for x in a], [int(x) for x in b], [int(x) for x in c]
+    want = {
+        "add": [(x + y) % P for x, y in zip(ai, bi)],
+        "sub": [(x - y) % P for x, y in zip(ai, bi)],
+        "mul": [(x * y) % P for x, y in zip(ai, bi)],
+        "mad": [(x * y + z) % P for x, y, z in zip(ai, bi, ci)],
+        "add_c": [(x + y) % P for x, y in zip(ai, bi)],
+        "sqr": [(x * x) % P for x in ai],
+        "canon": [x % P for x in ai],
+    }
+    for op, w in want.items():
+        got = glb.field_op_host(op, a, b, c)
+        assert np.array_equal(got, np.array(w, dtype=np.uint64)), op
+
+
+def test_poseidon_kats(glb, oracle, kats):
+    inp = np.stack([fib_vec(12), np.zeros(12, dtype=np.uint64)])
+    out = glb.hash_full_result_host(inp)
+    assert np.array_equal(out[0], kats["poseidon_fibonacci_state"]), hexs(out[0])
+    assert np.array_equal(out[1], kats["poseidon_zero_state"]), hexs(out[1])
+    rng = np.random.default_rng(2)
+    x = rng.integers(0, 2**64 - 1, size=(1000, 12), dtype=np.uint64, endpoint=True)  # non-canonical words too
+    x[0, :] = P - 1
+    x[1, :] = 2**64 - 1
+    out = glb.hash_full_result_host(x)
+    for i in range(0, 1000, 37):
+        assert np.array_equal(out[i], oracle.hash_full_result(x[i])), i
+    for i in (0, 1):
+        assert np.array_equal(out[i], oracle.hash_full_result(x[i])), i
+
+
+def test_linear_hash(glb, oracle, kats):
+    assert np.array_equal(glb.linear_hash_host(fib_vec(128)), kats["linear_hash_fibonacci_128"])
+    rng = np.random.default_rng(3)
+    for n in list(range(0, 26)) + [63, 64, 65, 127, 600, 665]:
+        v = rng.integers(0, P, size=n, dtype=np.uint64)
+        assert np.array_equal(glb.linear_hash_host(v), oracle.linear_hash(v)), n
+
+
+def test_merkletree_kats(glb, kats):
+    t = glb.merkletree_host(fib_rows(64, 128))
+    assert np.array_equal(t[-4:], kats["merkle_root_64x128"]), hexs(t[-4:])
+    t = glb.merkletree_host(np.zeros(0, dtype=np.uint64), nrows=64, ncols=0)
+    assert np.array_equal(t[-4:], kats["merkle_root_ncols0_64"])
+    t = glb.merkletree_host(np.zeros(0, dtype=np.uint64), nrows=1 << 17, ncols=0)
+    assert np.array_equal(t[-4:], kats["merkle_root_ncols0_131072"])
+
+
+def test_merkletree_every_node(glb, oracle, fixtures):
+    fin, fout, meta = fixtures["in"], fixtures["out"], fixtures["meta"]
+    for (h, w) in meta["tree"]:
+        k = "tree_%d_%d" % (h, w)
+        t = glb.merkletree_host(fin[k], nrows=h, ncols=w)
+        assert np.array_equal(t, fout[k]), k
+    rng = np.random.default_rng(4)
+    for (h, w) in [(2048, 13), (4096, 600), (1 << 15, 8), (512, 665)]:
+        a = rng.integers(0, 2**64 - 1, size=(h, w), dtype=np.uint64, endpoint=True)
+        assert np.array_equal(glb.merkletree_host(a), oracle.merkletree(a)), (h, w)
+
+
+def test_group_proofs(glb, oracle, fixtures):
+    fin, fout, meta = fixtures["in"], fixtures["out"], fixtures["meta"]
+    for (h, w, idx) in meta["proof"]:
+        src = fin["tree_%d_%d" % (h, w)]
+        ds = glb.DeviceBuffer(src.size).upload(src)
+        dt = glb.DeviceBuffer(glb.tree_num_elements(h))
+        glb.merkletree_dev(dt.ptr, ds.ptr, w, h)
+        got = glb.group_proof_dev(ds.ptr, dt.ptr, h, w, idx)
+        assert np.array_equal(got, fout["proof_%d_%d_%d" % (h, w, idx)]), (h, w, idx)
+
+
+def test_ntt_fixtures(glb, fixtures):
+    fin, fout, meta = fixtures["in"], fixtures["out"], fixtures["meta"]
+    for (n, c) in meta["ntt_shapes"]:
+        k = "%d_%d" % (n, c)
+        assert np.array_equal(glb.ntt_host(fin["ntt_" + k]), fout["ntt_" + k]), k
+        assert np.array_equal(glb.ntt_host(fin["ntt_" + k], inverse=True), fout["intt_" + k]), k
+
+
+@pytest.mark.parametrize("logn", list(range(0, 15)) + [16, 17])
+def test_ntt_vs_oracle_all_sizes(glb, oracle, logn):
+    rng = np.random.default_rng(100 + logn)
+    n = 1 << logn
+    for c in ([1, 7, 32, 45] if logn <= 12 else [33]):
+        a = rng.integers(0, 2**64 - 1, size=(n, c), dtype=np.uint64, endpoint=True)
+        f = glb.ntt_host(a)
+        assert np.array_equal(f, oracle.ntt(a)), (n, c, "fwd")
+        assert np.array_equal(glb.ntt_host(a, inverse=True), oracle.ntt(a, inverse=True)), (n, c, "inv")
+        assert np.array_equal(glb.ntt_host(a, inverse=True, extend=True), oracle.ntt(a, inverse=True, extend=True)), (n, c, "ext")
+        # NTT o INTT = id (reference tests.cpp:2225-2384), on canonical values
+        assert np.array_equal(glb.ntt_host(f, inverse=True), a % np.uint64(P)), (n, c, "roundtrip")
+
+
+def test_ntt_empty_is_noop(glb):
+    a = np.zeros((0, 4), dtype=np.uint64)
+    assert glb.ntt_host(a).shape == (0, 4)
+    assert glb.ntt_host(np.zeros((8, 0), dtype=np.uint64)).shape == (8, 0)
+
+
+def test_ntt_errors(glb):
+    with pytest.raises(glb.GLError):
+        glb.ntt_host(np.ones((12, 2), dtype=np.uint64))  # not a power of two (reference: assert, ntt_goldilocks.cpp:28)
+
+
+def test_ntt_dev_aliasing(glb, oracle):
+    """dst == src (in place) and dst != src (source preserved), as ntt_goldilocks.cpp:166-232."""
+    rng = np.random.default_rng(5)
+    n, c = 1 << 11, 40
+    a = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+    want = oracle.ntt(a)
+    s = glb.DeviceBuffer(a.size).upload(a)
+    d = glb.DeviceBuffer(a.size)
+    glb.ntt_dev(d.ptr, s.ptr, n, c)
+    assert np.array_equal(d.download().reshape(n, c), want)
+    assert np.array_equal(s.download().reshape(n, c), a)
+    glb.ntt_dev(s.ptr, s.ptr, n, c)
+    assert np.array_equal(s.download().reshape(n, c), want)
+
+
+def test_extend_pol_kats_and_fixtures(glb, kats, fixtures):
+    a = np.zeros((16, 8), dtype=np.uint64)
+    for j in range(8):
+        a[:, j] = fib_vec(16, 1 + j, 1 + j)
+    out = glb.extend_pol_host(a, 32)
+    assert np.array_equal(out[:, 0], kats["extendpol_16_to_32_col0"]), hexs(out[:, 0])
+    fin, fout, meta = fixtures["in"], fixtures["out"], fixtures["meta"]
+    for (n, e, c) in meta["lde"]:
+        k = "lde_%d_%d_%d" % (n, e, c)
+        assert np.array_equal(glb.extend_pol_host(fin[k], e), fout[k]), k
+
+
+def test_extend_pol_column_blocking(glb, oracle):
+    """A scratch limit forces several column blocks; the result must not change."""
+    rng = np.random.default_rng(6)
+    n, e, c = 1 << 10, 1 << 12, 100
+    a = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+    want = oracle.extend_pol(a, e)
+    glb.lib().gl_set_scratch_limit((n + e) * 8 * 32)
+    try:
+        assert np.array_equal(glb.extend_pol_host(a, e), want)
+    finally:
+        glb.lib().gl_set_scratch_limit(0)
+    assert np.array_equal(glb.extend_pol_host(a, e), want)
+
+
+def test_config1_commit_every_word(glb, oracle, kats):
+    """BASELINE.json configs[0]: 2^16 x 64 blowup 2.  Every extended element, every node, the root."""
+    n, e, c = 1 << 16, 1 << 17, 64
+    x, _ = oracle.xorshift(n * c)
+    x = x.reshape(n, c)
+    lde, tree, root = glb.commit_host(x, e)
+    assert np.array_equal(root, kats["config1_root_2p16x64_blowup2"]), hexs(root)
+    lde_o = oracle.extend_pol(x, e)
+    assert np.array_equal(lde, lde_o)
+    assert np.array_equal(tree, oracle.merkletree(lde_o))
+    assert np.array_equal(tree[-4:], root)
+
+
+def test_recursive_shape_high_blowup(glb, oracle):
+    """BASELINE.json configs[3] shape at reduced size: blowup 2^4."""
+    rng = np.random.default_rng(8)
+    n, e, c = 1 << 12, 1 << 16, 30
+    a = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+    lde, tree, root = glb.commit_host(a, e)
+    lde_o = oracle.extend_pol(a, e)
+    assert np.array_equal(lde, lde_o)
+    assert np.array_equal(tree, oracle.merkletree(lde_o))
+
+
+def _fib_matrix_mod_p(nrows, ncols):
+    """rows 0,1 = 1..ncols, row j = row j-1 + row j-2: element = (i+1) * Fib(j) mod p, vectorised."""
+    f = np.empty(nrows, dtype=np.uint64)
+    x, y = 1, 1
+    for j in range(nrows):
+        f[j] = x
+        x, y = y, (x + y) % P
+    k = np.arange(1, ncols + 1, dtype=np.uint64)
+    lo = (f & np.uint64(0xFFFFFFFF))[:, None] * k[None, :]          # < 2^39
+    hi = (f >> np.uint64(32))[:, None] * k[None, :]                 # < 2^39, weight 2^32
+    # value = lo + hi*2^32 = lo + (hi_lo << 32) + hi_hi * 2^64, and 2^64 = 2^32 - 1 (mod p)
+    hi_lo = hi & np.uint64(0xFFFFFFFF)
+    hi_hi = hi >> np.uint64(32)                                     # < 2^7
+    t = (hi_lo << np.uint64(32))                                    # < 2^64
+    u = lo + hi_hi * np.uint64(0xFFFFFFFF)                          # < 2^40
+    t = np.where(t >= np.uint64(P), t - np.uint64(P), t)
+    s = t + u                                                       # may wrap
+    wrapped = s < t
+    s = np.where(wrapped, s + np.uint64(0xFFFFFFFF), s)             # 2^64 = 2^32 - 1
+    return np.where(s >= np.uint64(P), s - np.uint64(P), s)
+
+
+def test_fib_matrix_helper_small():
+    assert np.array_equal(_fib_matrix_mod_p(200, 128), fib_rows(200, 128))
+
+
+def test_merkle_root_production_scale_kat(glb, kats):
+    """The reference's own full-size assertion (bench.cpp:440-443): 2^23 rows x 128 columns."""
+    nrows, ncols = 1 << 23, 128
+    dsrc = glb.DeviceBuffer(nrows * ncols)
+    step = 1 << 20
+    f = _fib_matrix_mod_p(nrows, ncols)
+    for r0 in range(0, nrows, step):
+        dsrc.upload(f[r0:r0 + step], word_offset=r0 * ncols)
+    del f
+    dtree = glb.DeviceBuffer(glb.tree_num_elements(nrows))
+    glb.merkletree_dev(dtree.ptr, dsrc.ptr, ncols, nrows)
+    root = dtree.download(4, glb.tree_num_elements(nrows) - 4)
+    assert np.array_equal(root, kats["merkle_root_2p23x128"]), hexs(root)
+
+
+def test_full_size_lde_sampled_columns_and_linearity(glb, oracle):
+    """2^22 -> 2^23 rows (size-independent properties at a large size): the LDE is column-independent,
+    so a few columns are checked against the oracle run on just those columns; plus linearity."""
+    n, e, c = 1 << 20, 1 << 21, 40
+    rng = np.random.default_rng(9)
+    a = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+    got = glb.extend_pol_host(a, e)
+    cols = [0, 17, 39]
+    want = oracle.extend_pol(np.ascontiguousarray(a[:, cols]), e)
+    assert np.array_equal(got[:, cols], want)
+    b = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+    gb = glb.extend_pol_host(b, e)
+    s = glb.field_op_host("add", a.reshape(-1), b.reshape(-1)).reshape(n, c)
+    gs = glb.extend_pol_host(s, e)
+    assert np.array_equal(gs.reshape(-1), glb.field_op_host("add", got.reshape(-1), gb.reshape(-1)))
