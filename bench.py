@@ -1,0 +1,313 @@
+#!/usr/bin/env python3
+"""bench.py -- STARK commit (LDE + Poseidon Merkle tree) throughput on B200.
+
+Metric (BASELINE.json): LDE + Poseidon-Merkle commit time and extended elements/s.
+One "step" = one stage commit of the workload: extendPol (INTT, coset shift 7, zero-pad, NTT over the
+extended domain) of every column followed by MerkleTreeGL::merkelize of the extended matrix
+(reference call sequence: src/starkpil/starks.cpp:52-56).
+
+  value      extended elements per second (E * ncols / step time), inputs resident in HBM
+  e2e        the same metric through the reference-facing C-ABI call gl_commit_host with HOST (pinned)
+             buffers: H2D of the trace, D2H of the extended matrix, the tree and the root inside the
+             timed region
+  roofline   for the dominant kernel (Poseidon leaf hashing) + per-phase entries under "phases"
+  cpu_baseline  the UNMODIFIED reference (oracle/_ref, OpenMP on all host cores) -- or the oracle port
+             when the reference was not compiled -- timed on a bounded sample of the same workload
+
+`--impl reference` times only that CPU arm, with the same JSON schema.
+Under torchrun (N>1) the workload is column-split over ranks for the LDE, exchanged to row blocks and
+each rank hashes its rows (weak scaling: every rank carries a full `workload` worth of columns/N ... see
+DESIGN.md "Multi-GPU").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (log2 rows N, log2 extended rows E, columns)
+    "c1": (16, 17, 64),     # BASELINE configs[0]: CPU-runnable synthetic commit
+    "c2": (23, 24, 600),    # BASELINE configs[1]: batch-proof stage-1 commit shape (the metric's config)
+    "c2_665": (23, 24, 665),  # same with the real fork_5 column count
+    "c4": (20, 24, 300),    # BASELINE configs[3]: recursive shape, blowup 2^4
+    "small": (18, 19, 64),
+}
+SEED = 1
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, index=0):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        pw = [float(r[2]) for r in self.rows if len(r) >= 7 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
+
+
+def lde_pass_bytes(logn, loge, ncols):
+    """Algorithmic bytes of all NTT passes of one extendPol in the current kernel plan: every pass over an
+    n x C matrix reads and writes it once (16 B per element); the first forward pass reads only the N
+    non-zero rows.  Pass counts follow csrc/glb200.cu run_ntt: ceil(log2 n / 8) passes (1 pass if <= 8)."""
+    def npass(k):
+        return 1 if k <= 8 else (k + 7) // 8
+    n, e = 1 << logn, 1 << loge
+    b = npass(logn) * 2 * n * ncols * 8
+    pe = npass(loge)
+    b += (n + e) * ncols * 8 + (pe - 1) * 2 * e * ncols * 8 if pe > 1 else (n + e) * ncols * 8
+    return b, npass(logn) + pe
+
+
+def permutations(loge, ncols):
+    e = 1 << loge
+    leaf = e * ((ncols + 7) // 8) if ncols > 4 else 0
+    return leaf, e - 1
+
+
+# --------------------------------------------------------------------------------------- CPU arm
+def cpu_arm(logn, loge, ncols, budget_s, steps, warmup):
+    """Reference CPU implementation on a bounded sample: same rows, fewer columns, all host threads."""
+    from oracle import pyoracle
+    r = pyoracle.ref(prefer_avx512=True)  # fastest build the host supports (AVX-512 Poseidon if avx512f, else the default AVX2)
+    kind = "reference" if r is not None else "port"
+    o = pyoracle.oracle()
+    cores = (r.L.ref_num_threads() if r is not None else o.L.glo_num_threads())
+    n, e = 1 << logn, 1 << loge
+    import __graft_entry__ as ge
+    glb = ge.load()
+
+    def run(cols):
+        x = glb.synthetic_host(n * cols, SEED).reshape(n, cols)
+        t0 = time.perf_counter()
+        if r is not None:
+            lde, tree, ms_lde, ms_tree = r.commit(x, e)
+            root = r.canon(tree[-4:])
+        else:
+            lde = o.extend_pol(x, e)
+            tree = o.merkletree(lde)
+            root = tree[-4:]
+            ms_lde = ms_tree = None
+        dt = time.perf_counter() - t0
+        return dt, root, ms_lde, ms_tree
+
+    # calibrate on 8 columns, then size the sample to the per-step budget (perm count per element kept close
+    # to the full workload's by preferring multiples of 8 columns)
+    dt8, _, _, _ = run(8)
+    per_col = dt8 / 8.0
+    cols = int(max(8, min(ncols, (budget_s / per_col) // 8 * 8)))
+    times = []
+    detail = None
+    for i in range(warmup + steps):
+        dt, root, a, b = run(cols)
+        if i >= warmup:
+            times.append(dt)
+            detail = (a, b)
+    best = float(np.mean(times)) if times else dt8
+    if not times:
+        cols = 8
+    return {
+        "value": e * cols / best, "unit": "ext-elem/s", "cores": int(cores), "kind": kind,
+        "sample": "2^%d rows x %d of %d columns -> 2^%d (same rows, column-reduced; LDE is column-independent, leaf hash cost is per 8 columns); extendPol + merkletree_%s, %d timed runs, mean %.2f s%s"
+                  % (logn, cols, ncols, loge, ("avx512" if (r is not None and r.avx512) else "avx"), len(times), best,
+                     "" if detail is None or detail[0] is None else " (LDE %.0f ms, tree %.0f ms)" % detail),
+        "ms_per_step_sample": best * 1e3,
+    }, best
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-budget", type=float, default=None, help="seconds of CPU work per reference step")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    logn, loge, ncols = WORKLOADS[args.workload]
+    n, e = 1 << logn, 1 << loge
+    hbm_peak, peak_src = peaks()
+    config = {"workload": "%s: stage commit 2^%d rows x %d cols, blowup %d -> 2^%d LDE + Poseidon Merkle tree" % (args.workload, logn, ncols, e // n, loge),
+              "log_rows": logn, "log_ext_rows": loge, "ncols": ncols, "parallelism": "1 process per GPU", "l2": "inputs >> L2 (126 MB): no flush needed"}
+
+    # ------------------------------------------------------------------ reference arm (CPU only)
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        total = max(1, args.steps + args.warmup)
+        budget = args.cpu_budget if args.cpu_budget else max(2.0, min(25.0, 150.0 / total))
+        cb, sec = cpu_arm(logn, loge, ncols, budget, args.steps, args.warmup)
+        line = {"impl": "reference", "metric": "commit_ext_elements_per_s", "value": cb["value"], "unit": "ext-elem/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step_sample"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "u64 (Goldilocks field)", "data": "synthetic", "config": config,
+                "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": cb["value"], "unit": "ext-elem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    # ------------------------------------------------------------------ B200 arm
+    import __graft_entry__ as ge
+    glb = ge.load()
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_
+        dist = dist_
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    glb.init(local_rank)
+
+    if world > 1:
+        import bench_mgpu
+        return bench_mgpu.run(args, glb, dist, rank, world, local_rank, config, WORKLOADS)
+
+    din = glb.DeviceBuffer(n * ncols)
+    dlde = glb.DeviceBuffer(e * ncols)
+    dtree = glb.DeviceBuffer(glb.tree_num_elements(e))
+    glb.fill_synthetic_dev(din.ptr, n * ncols, SEED)
+
+    for _ in range(args.warmup):
+        root = glb.commit_dev(dlde.ptr, dtree.ptr, din.ptr, e, n, ncols)
+    glb.lib().gl_sync()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    glb.kernel_launches(reset=True)
+    phase = {"lde_ms": 0.0, "leaf_ms": 0.0, "tree_ms": 0.0}
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        root = glb.commit_dev(dlde.ptr, dtree.ptr, din.ptr, e, n, ncols)  # synchronous; phases timed with CUDA events on the library stream
+        t = glb.last_timings()
+        for k in phase:
+            phase[k] += t[k]
+    glb.lib().gl_sync()
+    wall = time.perf_counter() - t0
+    launches = glb.kernel_launches()
+    clocks = sampler.stop()
+    dev_ms = sum(phase.values()) / args.steps          # CUDA-event time per step
+    for k in phase:
+        phase[k] /= args.steps
+    value = e * ncols / (dev_ms / 1e3)
+
+    # ---- roofline
+    leaf_perm, tree_perm = permutations(loge, ncols)
+    leaf_bytes = e * ncols * 8 + e * 32                 # read the extended matrix once, write the digests
+    lde_bytes, lde_passes = lde_pass_bytes(logn, loge, ncols)
+    roofline = {"kernel": "poseidon::k_linear_hash_rows (leaf hashing, %.0f%% of the step)" % (100 * phase["leaf_ms"] / dev_ms),
+                "bound": "hbm", "achieved": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                "frac": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "note": "integer-pipe bound, not HBM bound: %.3f G Poseidon permutations/s (see phases.leaf.int_pipe)" % (leaf_perm / phase["leaf_ms"] / 1e6)}
+    phases = {
+        "lde": {"ms": phase["lde_ms"], "kernels": "ntt::k_pass x %d passes per column block" % lde_passes, "bound": "hbm",
+                "algorithmic_bytes": lde_bytes, "achieved_GBps": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9,
+                "frac": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9 / hbm_peak},
+        "leaf": {"ms": phase["leaf_ms"], "permutations": leaf_perm, "Gperm_per_s": leaf_perm / phase["leaf_ms"] / 1e6},
+        "tree": {"ms": phase["tree_ms"], "permutations": tree_perm, "Gperm_per_s": tree_perm / max(phase["tree_ms"], 1e-9) / 1e6},
+    }
+
+    # ---- end to end through the host-pointer C ABI (pinned host buffers)
+    e2e = None
+    if not args.no_e2e:
+        import ctypes as C
+        hin, hlde, htree = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        in_b, lde_b, tree_b = n * ncols * 8, e * ncols * 8, glb.tree_num_elements(e) * 8
+        del din, dlde, dtree                                    # gl_commit_host allocates its own device buffers
+        L = glb.lib()
+        try:
+            for hp, sz in ((hin, in_b), (hlde, lde_b), (htree, tree_b)):
+                rc = L.gl_host_alloc(C.byref(hp), sz)
+                if rc != 0:
+                    raise glb.GLError(L.gl_last_error().decode())
+            tmp = glb.DeviceBuffer(n * ncols)
+            glb.fill_synthetic_dev(tmp.ptr, n * ncols, SEED)
+            L.gl_d2h(hin, C.c_void_p(tmp.ptr), in_b)
+            del tmp
+            u64p = C.POINTER(C.c_uint64)
+            root2 = np.zeros(4, dtype=np.uint64)
+            e2e_steps = max(1, min(args.steps, 3))
+            ts = []
+            for i in range(1 + e2e_steps):                       # 1 warm-up
+                t1 = time.perf_counter()
+                rc = L.gl_commit_host(C.cast(hlde, u64p), C.cast(htree, u64p), C.cast(hin, u64p), e, n, ncols,
+                                      root2.ctypes.data_as(u64p))
+                if rc != 0:
+                    raise glb.GLError(L.gl_last_error().decode())
+                if i > 0:
+                    ts.append(time.perf_counter() - t1)
+            assert np.array_equal(root2, root), "e2e root differs from the device-resident root"
+            e2e = {"value": e * ncols / float(np.mean(ts)), "unit": "ext-elem/s", "ms_per_step": float(np.mean(ts)) * 1e3,
+                   "h2d_bytes_per_step": in_b, "d2h_bytes_per_step": lde_b + tree_b + 32, "steps": e2e_steps,
+                   "call": "gl_commit_host(lde_out, tree_out, in, E, N, ncols, root) with cudaHostAlloc'ed buffers"}
+        except Exception as ex:  # not enough pinned host memory on this box etc.
+            e2e = {"value": None, "unit": "ext-elem/s", "error": str(ex)[:200], "h2d_bytes_per_step": in_b, "d2h_bytes_per_step": lde_b + tree_b + 32}
+        finally:
+            for hp in (hin, hlde, htree):
+                if hp.value:
+                    L.gl_host_free(hp)
+
+    # ---- CPU baseline on a bounded sample
+    cpu = None
+    if not args.no_cpu:
+        try:
+            cb, _ = cpu_arm(logn, loge, ncols, args.cpu_budget or 12.0, 1, 0)
+            cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as ex:
+            cpu = {"value": None, "unit": "ext-elem/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %s" % str(ex)[:160]}
+
+    line = {"metric": "commit_ext_elements_per_s", "value": value, "unit": "ext-elem/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms, "wall_ms_per_step": wall * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64 (Goldilocks field, integer pipe)", "data": "synthetic (splitmix64 of the element index mod p, generated in HBM)",
+            "config": config, "root": " ".join("%016X" % int(v) for v in root), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "roofline": roofline, "phases": phases, "cpu_baseline": cpu}
+    print(json.dumps(line))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

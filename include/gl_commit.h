@@ -101,6 +101,10 @@ int gl_linear_hash_host(uint64_t out[4], const uint64_t *in, uint64_t size);
  * out[i] is canonical.  b / c may be NULL when the op does not use them. */
 int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const uint64_t *c, uint64_t n, int op);
 
+/* Benchmark helper (not on the commit path): dst[i] = splitmix64(seed + (first_index+i)*0x9E3779B97F4A7C15)
+ * mod p, i < words; dst is a device pointer. */
+int gl_fill_synthetic_dev(uint64_t *dst, uint64_t words, uint64_t seed, uint64_t first_index);
+
 /* ---- layout helpers (merklehash_goldilocks.hpp:25-28, merkleTreeGL.hpp:71-78) ----------------- */
 uint64_t gl_tree_num_elements(uint64_t height);
 uint64_t gl_merkle_proof_size(uint64_t height);

@@ -55,6 +55,7 @@ SIGNATURES = {
     "gl_hash_full_result_host": (C.c_int, [_u64p, _u64p, _u64]),
     "gl_linear_hash_host": (C.c_int, [_u64p, _u64p, _u64]),
     "gl_field_op_host": (C.c_int, [_u64p, _u64p, _u64p, _u64p, _u64, C.c_int]),
+    "gl_fill_synthetic_dev": (C.c_int, [C.c_void_p, _u64, _u64, _u64]),
     "gl_tree_num_elements": (_u64, [_u64]),
     "gl_merkle_proof_size": (_u64, [_u64]),
     "gl_last_timings": (C.c_int, [C.POINTER(C.c_float)]),
@@ -258,3 +259,18 @@ def field_op_host(op, a, b=None, c=None):
     out = np.empty_like(a)
     _check(lib().gl_field_op_host(_p(out), _p(a), _p(b), _p(c), a.size, FIELD_OPS[op]))
     return out
+
+
+def fill_synthetic_dev(ptr, words, seed=1, first_index=0):
+    _check(lib().gl_fill_synthetic_dev(C.c_void_p(ptr), words, seed, first_index))
+
+
+def synthetic_host(words, seed=1, first_index=0):
+    """numpy twin of gl_fill_synthetic_dev (splitmix64 of the element index, mod p)."""
+    with np.errstate(over="ignore"):
+        i = np.arange(first_index, first_index + words, dtype=np.uint64)
+        z = np.uint64(seed) + i * np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return np.where(z >= np.uint64(P), z - np.uint64(P), z)

@@ -320,6 +320,20 @@ __global__ void k_field_op(u64 *out, const u64 *a, const u64 *b, const u64 *c, u
     out[i] = gl::canon(r);
 }
 
+// Synthetic benchmark input: word i = splitmix64(seed + i) mod p (counter based, so the CPU side can
+// regenerate any slice).  Not part of the commit path.
+__global__ void k_fill_synthetic(u64 *dst, u64 n, u64 seed, u64 first)
+{
+    u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        u64 z = seed + (first + i) * 0x9E3779B97F4A7C15ULL;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+        z = z ^ (z >> 31);
+        dst[i] = gl::canon(z);
+    }
+}
+
 struct DevBuf {
     void *p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -619,6 +633,17 @@ int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const 
     g.launches++;
     CU(cudaGetLastError());
     return gl_d2h(out, base + 3 * n, n * 8);
+}
+
+int gl_fill_synthetic_dev(uint64_t *dst, uint64_t words, uint64_t seed, uint64_t first_index)
+{
+    TRY(need_ctx());
+    if (words == 0) return GL_OK;
+    k_fill_synthetic<<<148 * 8, 256, 0, g.stream>>>((u64 *)dst, words, seed, first_index);
+    g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
 }
 
 } // extern "C"

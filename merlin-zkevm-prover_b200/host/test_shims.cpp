@@ -1,0 +1,112 @@
+// test_shims.cpp -- the reference's own commit-path tests, re-hosted on the drop-in classes
+// (no gtest in this image).  Mirrors src/goldilocks/tests/tests.cpp: merkletree_seq (:1817-1882),
+// ntt / ntt_block (:2225-2384), extendePol (:2554-2616), plus the stage-1 sequence of
+// Starks::genProof (starks.cpp:52-56) through MerkleTreeGL.  Exit code 0 = all passed.
+#include "merkleTreeGL.hpp"
+#include "ntt_goldilocks.hpp"
+#include <cstdio>
+#include <vector>
+
+static const uint64_t P = 0xFFFFFFFF00000001ULL;
+static int failures = 0;
+#define EXPECT_EQ(a, b) do { uint64_t a_ = (a), b_ = (b); if (a_ != b_) { printf("FAIL %s:%d %s = %016lX, want %016lX\n", __FILE__, __LINE__, #a, a_, b_); failures++; } } while (0)
+
+static Goldilocks::Element addm(Goldilocks::Element a, Goldilocks::Element b)
+{
+    unsigned __int128 s = (unsigned __int128)Goldilocks::toU64(a) + Goldilocks::toU64(b);
+    return Goldilocks::fromU64((uint64_t)(s % P));
+}
+
+static void test_merkletree()
+{
+    uint64_t ncols = 128, nrows = 1 << 6;
+    std::vector<Goldilocks::Element> cols(ncols * nrows);
+    for (uint64_t i = 0; i < ncols; i++) cols[i] = cols[i + ncols] = Goldilocks::fromU64(i + 1);
+    for (uint64_t j = 2; j < nrows; j++)
+        for (uint64_t i = 0; i < ncols; i++) cols[j * ncols + i] = addm(cols[(j - 2) * ncols + i], cols[(j - 1) * ncols + i]);
+    MerkleTreeGL mt(nrows, ncols, cols.data());
+    mt.merkelize();
+    Goldilocks::Element root[4];
+    mt.getRoot(root);
+    EXPECT_EQ(Goldilocks::toU64(root[0]), 0X918F7CD0C3E8701F);
+    EXPECT_EQ(Goldilocks::toU64(root[1]), 0X83A130E00F961B02);
+    EXPECT_EQ(Goldilocks::toU64(root[2]), 0X6921497B364123F8);
+    EXPECT_EQ(Goldilocks::toU64(root[3]), 0XBD2B98A57B748BF4);
+    // proof = row || siblings; recompute nothing, just check sizes and that sibling 0 is the neighbour leaf
+    std::vector<Goldilocks::Element> proof(ncols + mt.MerkleProofSize() * HASH_SIZE);
+    mt.getGroupProof(proof.data(), 5);
+    EXPECT_EQ(mt.MerkleProofSize(), 6);
+    for (int k = 0; k < 4; k++) EXPECT_EQ(Goldilocks::toU64(proof[ncols + k]), Goldilocks::toU64(mt.nodes[4 * 4 + k]));
+    EXPECT_EQ(Goldilocks::toU64(proof[3]), Goldilocks::toU64(cols[5 * ncols + 3]));
+    // edge: ncols = 0 (tests.cpp:1851-1865)
+    MerkleTreeGL mt0(nrows, 0, NULL);
+    mt0.merkelize();
+    mt0.getRoot(root);
+    EXPECT_EQ(Goldilocks::toU64(root[0]), 0X25225F1A5D49614A);
+    EXPECT_EQ(Goldilocks::toU64(root[3]), 0X49561260080D30C3);
+}
+
+static void test_ntt_roundtrip()
+{
+    const uint64_t n = 1 << 4, ncols = 8;
+    std::vector<Goldilocks::Element> a(n * ncols), init(n * ncols), b(n * ncols);
+    for (uint64_t j = 0; j < ncols; j++) a[j] = a[ncols + j] = Goldilocks::fromU64(1 + j);
+    for (uint64_t i = 2; i < n; i++)
+        for (uint64_t j = 0; j < ncols; j++) a[i * ncols + j] = addm(a[(i - 1) * ncols + j], a[(i - 2) * ncols + j]);
+    init = a;
+    NTT_Goldilocks gntt(n);
+    for (int rep = 0; rep < 3; rep++) { // dst == src
+        gntt.NTT(a.data(), a.data(), n, ncols);
+        gntt.INTT(a.data(), a.data(), n, ncols);
+    }
+    for (uint64_t i = 0; i < n * ncols; i++) EXPECT_EQ(Goldilocks::toU64(a[i]), Goldilocks::toU64(init[i]));
+    gntt.NTT(b.data(), a.data(), n, ncols, NULL, 4, 3); // dst != src, odd nphase/nblock are only hints
+    for (uint64_t i = 0; i < n * ncols; i++) EXPECT_EQ(Goldilocks::toU64(a[i]), Goldilocks::toU64(init[i]));
+    gntt.INTT(NULL, b.data(), n, ncols);                // dst == NULL: in place
+    for (uint64_t i = 0; i < n * ncols; i++) EXPECT_EQ(Goldilocks::toU64(b[i]), Goldilocks::toU64(init[i]));
+    gntt.NTT(a.data(), a.data(), 0, ncols);             // size 0 / ncols 0: no-op
+    gntt.NTT(a.data(), a.data(), n, 0);
+    bool thrown = false;
+    try { NTT_Goldilocks big((uint64_t)1 << 33); } catch (const std::range_error &) { thrown = true; }
+    EXPECT_EQ(thrown ? 1 : 0, 1);
+}
+
+static void test_extendPol_and_stage_commit()
+{
+    const uint64_t N = 1 << 4, NE = 1 << 5, ncols = 8;
+    std::vector<Goldilocks::Element> a(NE * ncols), scratch(NE * ncols);
+    for (uint64_t j = 0; j < ncols; j++) a[j] = a[ncols + j] = Goldilocks::fromU64(1 + j);
+    for (uint64_t i = 2; i < N; i++)
+        for (uint64_t j = 0; j < ncols; j++) a[i * ncols + j] = addm(a[(i - 1) * ncols + j], a[(i - 2) * ncols + j]);
+    NTT_Goldilocks ntt(N);
+    ntt.extendPol(a.data(), a.data(), NE, N, ncols, scratch.data()); // input == output, as tests.cpp:2578
+    const uint64_t want[32] = {
+        0X3E7CA26D67147C31, 0X1310720153E0ABE4, 0X20446D2EA50E8F96};
+    for (int k = 0; k < 3; k++) EXPECT_EQ(Goldilocks::toU64(a[k * ncols]), want[k]);
+    // stage commit as Starks::genProof does it (starks.cpp:52-56): tree over the extended matrix
+    MerkleTreeGL tree(NE, ncols, a.data());
+    tree.merkelize();
+    Goldilocks::Element r1[4], r2[4];
+    tree.getRoot(r1);
+    std::vector<Goldilocks::Element> nodes(tree.getTreeNumElements());
+    PoseidonGoldilocks::merkletree_seq(nodes.data(), a.data(), ncols, NE);
+    std::memcpy(r2, &nodes[nodes.size() - 4], sizeof r2);
+    for (int k = 0; k < 4; k++) EXPECT_EQ(Goldilocks::toU64(r1[k]), Goldilocks::toU64(r2[k]));
+}
+
+int main()
+{
+    try
+    {
+        test_merkletree();
+        test_ntt_roundtrip();
+        test_extendPol_and_stage_commit();
+    }
+    catch (const std::exception &e)
+    {
+        printf("FAIL exception: %s\n", e.what());
+        return 2;
+    }
+    printf(failures ? "%d FAILURES\n" : "shim tests passed\n", failures);
+    return failures ? 1 : 0;
+}
