@@ -39,6 +39,7 @@ WORKLOADS = {
     "c2_665": (23, 24, 665),  # same with the real fork_5 column count
     "c4": (20, 24, 300),    # BASELINE configs[3]: recursive shape, blowup 2^4
     "small": (18, 19, 64),
+    "mid": (20, 21, 256),    # profiling shape: row pitch 2 KiB, fits ncu kernel replay
 }
 SEED = 1
 
