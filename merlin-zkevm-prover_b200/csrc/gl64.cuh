@@ -29,6 +29,20 @@ struct u128 {
     u32 x0, x1, x2, x3;
 };
 
+// 2^32 - 1 read from constant memory so that ptxas keeps x*(2^32-1)+y as ONE IMAD.WIDE.U32 with a
+// carry-out predicate; with an immediate it strength-reduces to IMAD.IADD + IMAD.HI (half rate).
+__constant__ u32 c_eps[2] = {0xFFFFFFFFu, 0u};
+
+// acc += a * b (32x32 -> 64, no overflow expected by the caller).  Written as a carry chain: ptxas
+// fuses the pair into one IMAD.WIDE.U32 with the accumulator as addend and, unlike mad.wide.u32,
+// does not re-associate a chain of them into multiplies + 3-input adds.
+__device__ __forceinline__ void madw(u64 &acc, u32 a, u32 b)
+{
+    u32 lo = (u32)acc, hi = (u32)(acc >> 32);
+    asm("mad.lo.cc.u32 %0, %2, %3, %0;\n\tmadc.hi.u32 %1, %2, %3, %1;" : "+r"(lo), "+r"(hi) : "r"(a), "r"(b));
+    acc = ((u64)hi << 32) | lo;
+}
+
 __device__ __forceinline__ u64 pack(u32 lo, u32 hi) { return ((u64)hi << 32) | lo; }
 
 __device__ __forceinline__ u64 canon(u64 x) { return x >= P ? x - P : x; }
@@ -97,8 +111,8 @@ __device__ __forceinline__ u64 reduce128(u128 x)
         "sub.cc.u32 %0, %2, %5;\n\t"
         "subc.cc.u32 %1, %3, 0;\n\t"
         "subc.u32 b, 0, 0;\n\t"                      // b = -borrow
-        "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %0;\n\t"
-        "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %1;\n\t"
+        "mad.lo.cc.u32 %0, %4, %6, %0;\n\t"
+        "madc.hi.cc.u32 %1, %4, %6, %1;\n\t"
         "addc.u32 k, b, 0;\n\t"                      // k = carry - borrow
         "neg.s32 kl, k;\n\t"
         "shr.s32 kh, k, 31;\n\t"
@@ -106,7 +120,7 @@ __device__ __forceinline__ u64 reduce128(u128 x)
         "addc.u32 %1, %1, kh;\n\t"
         "}"
         : "=&r"(r0), "=&r"(r1)
-        : "r"(x.x0), "r"(x.x1), "r"(x.x2), "r"(x.x3));
+        : "r"(x.x0), "r"(x.x1), "r"(x.x2), "r"(x.x3), "r"(c_eps[0]));
     return pack(r0, r1);
 }
 
@@ -116,17 +130,66 @@ __device__ __forceinline__ u64 reduce96(u32 x0, u32 x1, u32 x2)
     u32 r0, r1;
     asm("{\n\t"
         ".reg .u32 k;\n\t"
-        "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %2;\n\t"
-        "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %3;\n\t"
+        "mad.lo.cc.u32 %0, %4, %5, %2;\n\t"
+        "madc.hi.cc.u32 %1, %4, %5, %3;\n\t"
         "addc.u32 k, 0, 0;\n\t"
         "neg.s32 k, k;\n\t"                          // 0 or 0xFFFFFFFF
         "add.cc.u32 %0, %0, k;\n\t"
         "addc.u32 %1, %1, 0;\n\t"
         "}"
         : "=&r"(r0), "=&r"(r1)
-        : "r"(x0), "r"(x1), "r"(x2));
+        : "r"(x0), "r"(x1), "r"(x2), "r"(c_eps[0]));
     return pack(r0, r1);
 }
+
+// 160-bit input x0 + x1 2^32 + x2 2^64 + x3 2^96 + x4 2^128 with x4 < 2^31 (2^128 = -2^32 mod p):
+//   {x0,x1} - {x3,x4} + x2*(2^32-1); same single net correction as reduce128.
+__device__ __forceinline__ u64 reduce160(u32 x0, u32 x1, u32 x2, u32 x3, u32 x4)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 b, k, kl, kh;\n\t"
+        "sub.cc.u32 %0, %2, %5;\n\t"
+        "subc.cc.u32 %1, %3, %6;\n\t"
+        "subc.u32 b, 0, 0;\n\t"
+        "mad.lo.cc.u32 %0, %4, %7, %0;\n\t"
+        "madc.hi.cc.u32 %1, %4, %7, %1;\n\t"
+        "addc.u32 k, b, 0;\n\t"
+        "neg.s32 kl, k;\n\t"
+        "shr.s32 kh, k, 31;\n\t"
+        "add.cc.u32 %0, %0, kl;\n\t"
+        "addc.u32 %1, %1, kh;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(x4), "r"(c_eps[0]));
+    return pack(r0, r1);
+}
+
+// Lazy dot-product accumulator: sum of up to 32 products a*c with a any u64 and c a constant < 2^64
+// given as limbs c = l0 + l1 2^22 + l2 2^43 (22/21/21 bits).  Six 64-bit column sums (a half x limb
+// < 2^54), no carries while accumulating; one fold() per dot product.
+struct Dot {
+    u64 c00, c01, c02, c10, c11, c12;
+    __device__ __forceinline__ void zero() { c00 = c01 = c02 = c10 = c11 = c12 = 0; }
+    __device__ __forceinline__ void mad(u64 a, u32 l0, u32 l1, u32 l2)
+    {
+        u32 a0 = (u32)a, a1 = (u32)(a >> 32);
+        madw(c00, a0, l0); madw(c01, a0, l1); madw(c02, a0, l2);
+        madw(c10, a1, l0); madw(c11, a1, l1); madw(c12, a1, l2);
+    }
+    __device__ __forceinline__ u64 fold() const
+    {
+        typedef unsigned __int128 w128;
+        w128 i0 = (w128)c00 + ((w128)c01 << 22) + ((w128)c02 << 43);
+        w128 i1 = (w128)c10 + ((w128)c11 << 22) + ((w128)c12 << 43);
+        u64 lo = (u64)i0, hi = (u64)(i0 >> 64), l1 = (u64)i1, h1 = (u64)(i1 >> 64);
+        u32 x0 = (u32)lo, x1 = (u32)(lo >> 32), x2 = (u32)hi, x3 = (u32)(hi >> 32), x4;
+        asm("add.cc.u32 %0, %0, %4;\n\taddc.cc.u32 %1, %1, %5;\n\taddc.cc.u32 %2, %2, %6;\n\taddc.u32 %3, %7, 0;"
+            : "+r"(x1), "+r"(x2), "+r"(x3), "=r"(x4)
+            : "r"((u32)l1), "r"((u32)(l1 >> 32)), "r"((u32)h1), "r"((u32)(h1 >> 32)));
+        return reduce160(x0, x1, x2, x3, x4);
+    }
+};
 
 __device__ __forceinline__ u64 mul(u64 a, u64 b) { return reduce128(mul_wide(a, b)); }
 __device__ __forceinline__ u64 sqr(u64 a) { return reduce128(mul_wide(a, a)); }

@@ -1,16 +1,24 @@
-// poseidon.cuh -- Poseidon-Goldilocks permutation, sponge and Merkle kernels for sm_100a.
+// poseidon.cuh -- Poseidon-Goldilocks permutation for sm_100a.
 //
 // Replaces (reference, CPU AVX2/AVX-512):
 //   PoseidonGoldilocks::hash_full_result   src/goldilocks/src/poseidon_goldilocks.cpp:166-228 (seq: 5-37)
-//   PoseidonGoldilocks::linear_hash        poseidon_goldilocks.cpp:229-265
-//   PoseidonGoldilocks::merkletree_avx     poseidon_goldilocks.cpp:266-301
 //
-// Mapping: one thread owns one 12-word state in registers (24 x 32-bit); all lanes of a warp
-// execute the same round, so round constants / sparse matrices are read from __constant__
-// memory as warp-uniform operands.  Work per permutation: 118 S-boxes (x^7 = 4 modmuls, the
-// round constant rides on the last multiply as a fused multiply-add), 7 circulant MDS layers
-// done on 32-bit halves with one lazy reduction per output, one dense 12x12 layer and 22
-// sparse partial rounds.  Integer-pipe bound; HBM traffic is 8 B per absorbed element.
+// Mapping: one thread owns one 12-word state in registers; all lanes of a warp execute the same
+// round, so round constants / matrices are warp-uniform operands read from __constant__ memory.
+//
+// What the measured machine dictates (profiles/r1_01_ubench.txt, profiles/r1_01_leaf_ncu.txt):
+//   * IMAD.WIDE issues at 16 lanes/clk/SMSP (2 clk per warp instruction), IADD3-class at ~22
+//     lanes/clk/SMSP, and the two do NOT overlap in practice: cost ~ 2*#IMAD + 1.5*#ALU clocks.
+//     So every instruction counts; a modular multiply is 5 IMAD.WIDE + 11 ALU (~26 clk).
+//   * The first version (88 KB of straight-line SASS) stalled mostly on instruction fetch
+//     ("no_instruction" was the top stall).  All 8 full rounds now share ONE loop body and the 22
+//     partial rounds another; the whole permutation is ~30 KB of SASS.
+//   * Dot products against 64-bit constants (the dense pre-partial matrix and the 12-term row of
+//     every partial round) are accumulated lazily in six carry-free 64-bit columns (gl::Dot: the
+//     constant is pre-split into 22/21/21-bit limbs, 6 IMAD.WIDE per product, no ALU work) and
+//     reduced once per dot product instead of once per term.
+//   * The circulant MDS layers use the small entries (< 64) directly: 24 IMAD.WIDE per output on
+//     32-bit halves and one 96-bit reduction.
 #pragma once
 #include "gl64.cuh"
 #include "poseidon_constants.cuh"
@@ -20,9 +28,13 @@ namespace poseidon {
 using gl::u32;
 using gl::u64;
 
-__constant__ u64 c_RC[118];
-__constant__ u64 c_PM[144];
-__constant__ u64 c_SP[506];
+// Tables derived from GLP_RC / GLP_PM / GLP_SP by upload_constants() (poseidon_kernels.cuh):
+__constant__ u64 c_RC0[12];          // pre-round constants C[0..12)
+__constant__ u64 c_RCF[8 * 12];      // constants added after the S-box of full round r (row 7 = 0)
+__constant__ u64 c_RCP[22];          // partial-round constants C[60..82)
+__constant__ uint4 c_PL[12 * 12];    // dense layer: limbs of P[j][i] at [i*12 + j] (x,y,z; w unused)
+__constant__ uint4 c_SL[22 * 12];    // partial round r: limbs of the dot row S[23r + i] at [r*12 + i]
+__constant__ u64 c_SV[22 * 11];      // partial round r: rank-1 column S[23r + 12 + i], i < 11
 
 // MDS circulant (reference M[j][i] = circ[(i-j) mod 12] + 8*[i==j==0]) as immediates.
 __device__ __forceinline__ constexpr u32 mds_entry(int j, int i)
@@ -31,7 +43,7 @@ __device__ __forceinline__ constexpr u32 mds_entry(int j, int i)
     return circ[(i - j + 12) % 12] + ((i == 0 && j == 0) ? 8u : 0u);
 }
 
-// x^7 + c   (c canonical)
+// x^7 + c   (c any representative)
 __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
 {
     u64 x2 = gl::sqr(x);
@@ -40,16 +52,8 @@ __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
     return gl::mad(x3, x4, c);
 }
 
-__device__ __forceinline__ u64 sbox(u64 x)
-{
-    u64 x2 = gl::sqr(x);
-    u64 x3 = gl::mul(x, x2);
-    u64 x4 = gl::sqr(x2);
-    return gl::mul(x3, x4);
-}
-
 // new[i] = sum_j M[j][i] old[j]  (poseidon_goldilocks.hpp:148-162).  Entries < 64, so the sums of
-// the low and of the high 32-bit halves each fit 64 bits (< 2^41); one 96-bit reduction per output.
+// the low and of the high 32-bit halves each fit 64 bits (< 2^42); one 96-bit reduction per output.
 __device__ __forceinline__ void mds_layer(u64 (&s)[12])
 {
     u32 lo[12], hi[12];
@@ -63,15 +67,15 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
         u64 L = 0, H = 0;
 #pragma unroll
         for (int j = 0; j < 12; j++) {
-            L += (u64)lo[j] * mds_entry(j, i);
-            H += (u64)hi[j] * mds_entry(j, i);
+            gl::madw(L, lo[j], mds_entry(j, i));
+            gl::madw(H, hi[j], mds_entry(j, i));
         }
-        u64 t = (L >> 32) + H; // < 2^42
+        u64 t = (L >> 32) + H; // < 2^43
         s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
     }
 }
 
-// Dense layer before the partial rounds: new[i] = sum_j PM[j*12+i] old[j].
+// Dense layer before the partial rounds: new[i] = sum_j P[j][i] old[j]   (poseidon_goldilocks.cpp:17)
 __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 {
     u64 o[12];
@@ -79,12 +83,41 @@ __device__ __forceinline__ void dense_layer(u64 (&s)[12])
     for (int j = 0; j < 12; j++) o[j] = s[j];
 #pragma unroll 1
     for (int i = 0; i < 12; i++) {
-        u64 acc = gl::mul(o[0], c_PM[i]);
+        gl::Dot d;
+        d.zero();
 #pragma unroll
-        for (int j = 1; j < 12; j++) acc = gl::mad(o[j], c_PM[j * 12 + i], acc);
-        // dynamic register indexing is avoided by a rotating write below
+        for (int j = 0; j < 12; j++) {
+            const uint4 l = c_PL[i * 12 + j];
+            d.mad(o[j], l.x, l.y, l.z);
+        }
+        const u64 acc = d.fold();
+        // rotate instead of indexing registers dynamically: after 12 steps s[] holds new[0..12)
         s[0] = s[1]; s[1] = s[2]; s[2] = s[3]; s[3] = s[4]; s[4] = s[5]; s[5] = s[6];
         s[6] = s[7]; s[7] = s[8]; s[8] = s[9]; s[9] = s[10]; s[10] = s[11]; s[11] = acc;
+    }
+}
+
+// 22 partial rounds (poseidon_goldilocks.cpp:19-28): t = s0^7 + C; s0' = <(t, s1..s11), S_row>;
+// s_i += t * S_col[i].
+__device__ __forceinline__ void partial_rounds(u64 (&s)[12])
+{
+#pragma unroll 1
+    for (int r = 0; r < 22; r++) {
+        const u64 t = sbox_add(s[0], c_RCP[r]);
+        gl::Dot d;
+        d.zero();
+        {
+            const uint4 l = c_SL[r * 12];
+            d.mad(t, l.x, l.y, l.z);
+        }
+#pragma unroll
+        for (int i = 1; i < 12; i++) {
+            const uint4 l = c_SL[r * 12 + i];
+            d.mad(s[i], l.x, l.y, l.z);
+        }
+#pragma unroll
+        for (int i = 1; i < 12; i++) s[i] = gl::mad(t, c_SV[r * 11 + i - 1], s[i]);
+        s[0] = d.fold();
     }
 }
 
@@ -92,36 +125,18 @@ __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 __device__ __forceinline__ void permute(u64 (&s)[12])
 {
 #pragma unroll
-    for (int i = 0; i < 12; i++) s[i] = gl::add_c(s[i], c_RC[i]);
+    for (int i = 0; i < 12; i++) s[i] = gl::add_c(s[i], c_RC0[i]);
 #pragma unroll 1
-    for (int r = 0; r < 3; r++) {
+    for (int r = 0; r < 8; r++) {
 #pragma unroll
-        for (int i = 0; i < 12; i++) s[i] = sbox_add(s[i], c_RC[(r + 1) * 12 + i]);
-        mds_layer(s);
+        for (int i = 0; i < 12; i++) s[i] = sbox_add(s[i], c_RCF[r * 12 + i]);
+        if (r == 3) {
+            dense_layer(s);
+            partial_rounds(s);
+        } else {
+            mds_layer(s);
+        }
     }
-#pragma unroll
-    for (int i = 0; i < 12; i++) s[i] = sbox_add(s[i], c_RC[48 + i]);
-    dense_layer(s);
-#pragma unroll 1
-    for (int r = 0; r < 22; r++) {
-        const u64 *S = &c_SP[23 * r];
-        u64 t = sbox_add(s[0], c_RC[60 + r]);
-        u64 d = gl::mul(t, S[0]);
-#pragma unroll
-        for (int i = 1; i < 12; i++) d = gl::mad(s[i], S[i], d);
-#pragma unroll
-        for (int i = 1; i < 12; i++) s[i] = gl::mad(t, S[11 + i], s[i]);
-        s[0] = d;
-    }
-#pragma unroll 1
-    for (int r = 0; r < 3; r++) {
-#pragma unroll
-        for (int i = 0; i < 12; i++) s[i] = sbox_add(s[i], c_RC[82 + 12 * r + i]);
-        mds_layer(s);
-    }
-#pragma unroll
-    for (int i = 0; i < 12; i++) s[i] = sbox(s[i]);
-    mds_layer(s);
 }
 
 } // namespace poseidon

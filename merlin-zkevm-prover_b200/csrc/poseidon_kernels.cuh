@@ -78,12 +78,30 @@ __global__ void __launch_bounds__(kThreads) k_tree_level(u64 *__restrict__ paren
     o[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
 }
 
+// Derive the device tables from the generated parameter header (poseidon_constants.cuh).
 inline cudaError_t upload_constants()
 {
+    static u64 rc0[12], rcf[96], rcp[22], sv[22 * 11];
+    static uint4 pl[144], sl[22 * 12];
+    auto limbs = [](u64 c) { return make_uint4((u32)(c & 0x3FFFFF), (u32)((c >> 22) & 0x1FFFFF), (u32)(c >> 43), 0u); };
+    for (int i = 0; i < 12; i++) rc0[i] = GLP_RC[i];
+    for (int r = 0; r < 8; r++)
+        for (int i = 0; i < 12; i++)
+            rcf[r * 12 + i] = r < 4 ? GLP_RC[(r + 1) * 12 + i] : (r < 7 ? GLP_RC[82 + 12 * (r - 4) + i] : 0);
+    for (int r = 0; r < 22; r++) {
+        rcp[r] = GLP_RC[60 + r];
+        for (int i = 0; i < 12; i++) sl[r * 12 + i] = limbs(GLP_SP[23 * r + i]);
+        for (int i = 0; i < 11; i++) sv[r * 11 + i] = GLP_SP[23 * r + 12 + i];
+    }
+    for (int i = 0; i < 12; i++)
+        for (int j = 0; j < 12; j++) pl[i * 12 + j] = limbs(GLP_PM[j * 12 + i]);
     cudaError_t e;
-    if ((e = cudaMemcpyToSymbol(c_RC, GLP_RC, sizeof(GLP_RC))) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_PM, GLP_PM, sizeof(GLP_PM))) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_SP, GLP_SP, sizeof(GLP_SP))) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_RC0, rc0, sizeof rc0)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_RCF, rcf, sizeof rcf)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_RCP, rcp, sizeof rcp)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_PL, pl, sizeof pl)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_SL, sl, sizeof sl)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_SV, sv, sizeof sv)) != cudaSuccess) return e;
     return cudaSuccess;
 }
 
