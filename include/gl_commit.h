@@ -113,6 +113,32 @@ uint64_t gl_merkle_proof_size(uint64_t height);
  *      (CUDA events on the library stream), in milliseconds: [0] LDE, [1] leaf hashing, [2] tree levels */
 int gl_last_timings(float ms[3]);
 
+/* [0] LDE, [1] leaf hashing, [2] tree levels (incl. the gathered top), [3] multi-GPU exchange */
+int gl_last_timings4(float ms[4]);
+
+/* ---- multi-GPU: one process per GPU (the reference is single-process OpenMP and has no
+ *      counterpart).  Columns are split over ranks for extendPol (ntt_goldilocks.cpp:326-352 is
+ *      column-independent), an NCCL all-to-all over NVLink turns column blocks into row blocks, each
+ *      rank hashes its E/world rows (poseidon_goldilocks.cpp:277-281) and builds its subtree
+ *      (:283-300); the world subtree roots are gathered and the top log2(world) levels hashed on every
+ *      rank.  Result: the same root and node values as the single-GPU call.
+ *      Rank r owns columns [gl_mgpu_col_start(C, world, r), gl_mgpu_col_start(C, world, r+1)). */
+int gl_mgpu_unique_id(uint8_t id[128]);                      /* rank 0; broadcast the 128 bytes to all ranks */
+int gl_mgpu_init(const uint8_t id[128], int rank, int world); /* after gl_init(device); world in {1,2,4,8} */
+int gl_mgpu_shutdown(void);
+uint64_t gl_mgpu_col_start(uint64_t ncols, int world, int rank);
+/* in_cols: n x w (this rank's w columns, row-major, pitch w); lde_cols: n_ext x w (out: this rank's
+ * columns of the LDE); row_panels: (n_ext/world) * ncols_total words (out: this rank's rows, stored as
+ * `world` panels -- panel p at word offset (n_ext/world)*col_start(p), row-major with pitch w_p);
+ * subtree: (2*n_ext/world - 1)*4 words (out); root: HOST pointer, 4 words (same on every rank). */
+int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, const uint64_t *in_cols,
+                   uint64_t n_ext, uint64_t n, uint64_t ncols_total, uint64_t root[4]);
+/* Assemble the full (2*n_ext-1)*4-word node array (MerkleTreeGL::nodes layout) on every rank. */
+int gl_mgpu_gather_tree(uint64_t *tree_full, const uint64_t *subtree, uint64_t n_ext);
+/* Benchmark helper: the column range [col0, col0+ncols_local) of gl_fill_synthetic_dev's matrix. */
+int gl_fill_synthetic_cols_dev(uint64_t *dst, uint64_t nrows, uint64_t col0, uint64_t ncols_local,
+                               uint64_t ncols_total, uint64_t seed);
+
 #ifdef __cplusplus
 }
 #endif

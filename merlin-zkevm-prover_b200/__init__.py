@@ -59,6 +59,14 @@ SIGNATURES = {
     "gl_tree_num_elements": (_u64, [_u64]),
     "gl_merkle_proof_size": (_u64, [_u64]),
     "gl_last_timings": (C.c_int, [C.POINTER(C.c_float)]),
+    "gl_last_timings4": (C.c_int, [C.POINTER(C.c_float)]),
+    "gl_mgpu_unique_id": (C.c_int, [C.POINTER(C.c_uint8)]),
+    "gl_mgpu_init": (C.c_int, [C.POINTER(C.c_uint8), C.c_int, C.c_int]),
+    "gl_mgpu_shutdown": (C.c_int, []),
+    "gl_mgpu_col_start": (_u64, [_u64, C.c_int, C.c_int]),
+    "gl_commit_mgpu": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64p]),
+    "gl_mgpu_gather_tree": (C.c_int, [C.c_void_p, C.c_void_p, _u64]),
+    "gl_fill_synthetic_cols_dev": (C.c_int, [C.c_void_p, _u64, _u64, _u64, _u64, _u64]),
 }
 
 
@@ -122,6 +130,12 @@ def last_timings():
     ms = (C.c_float * 3)()
     lib().gl_last_timings(ms)
     return {"lde_ms": ms[0], "leaf_ms": ms[1], "tree_ms": ms[2]}
+
+
+def last_timings4():
+    ms = (C.c_float * 4)()
+    lib().gl_last_timings4(ms)
+    return {"lde_ms": ms[0], "leaf_ms": ms[1], "tree_ms": ms[2], "exchange_ms": ms[3]}
 
 
 def tree_num_elements(height):
@@ -274,3 +288,35 @@ def synthetic_host(words, seed=1, first_index=0):
         z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
         z = z ^ (z >> np.uint64(31))
     return np.where(z >= np.uint64(P), z - np.uint64(P), z)
+
+
+# ---- multi-GPU (one process per GPU) ---------------------------------------------------------------
+def mgpu_unique_id():
+    """128-byte NCCL unique id (call on rank 0, broadcast to every rank)."""
+    buf = (C.c_uint8 * 128)()
+    _check(lib().gl_mgpu_unique_id(buf))
+    return bytes(buf)
+
+
+def mgpu_init(unique_id, rank, world):
+    buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+    _check(lib().gl_mgpu_init(buf, rank, world))
+
+
+def mgpu_shutdown():
+    lib().gl_mgpu_shutdown()
+
+
+def commit_mgpu(lde_cols, row_panels, subtree, in_cols, n_ext, n, ncols_total):
+    root = np.zeros(4, dtype=np.uint64)
+    _check(lib().gl_commit_mgpu(C.c_void_p(lde_cols), C.c_void_p(row_panels), C.c_void_p(subtree), C.c_void_p(in_cols),
+                                n_ext, n, ncols_total, _p(root)))
+    return root
+
+
+def mgpu_gather_tree(tree_full, subtree, n_ext):
+    _check(lib().gl_mgpu_gather_tree(C.c_void_p(tree_full), C.c_void_p(subtree), n_ext))
+
+
+def fill_synthetic_cols_dev(ptr, nrows, col0, ncols_local, ncols_total, seed=1):
+    _check(lib().gl_fill_synthetic_cols_dev(C.c_void_p(ptr), nrows, col0, ncols_local, ncols_total, seed))

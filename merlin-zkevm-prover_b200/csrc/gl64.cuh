@@ -191,8 +191,17 @@ struct Dot {
     }
 };
 
-__device__ __forceinline__ u64 mul(u64 a, u64 b) { return reduce128(mul_wide(a, b)); }
-__device__ __forceinline__ u64 sqr(u64 a) { return reduce128(mul_wide(a, a)); }
+// nvcc's native 128-bit product is one instruction shorter than mul_wide (the cross-term carry rides
+// on IMAD.WIDE.U32.X instead of a SEL): 4 IMAD.WIDE + 3 ALU, then the 8-instruction reduction.
+__device__ __forceinline__ u128 mul_wide_native(u64 a, u64 b)
+{
+    const unsigned __int128 x = (unsigned __int128)a * b;
+    u128 r;
+    r.x0 = (u32)x; r.x1 = (u32)(x >> 32); r.x2 = (u32)(x >> 64); r.x3 = (u32)(x >> 96);
+    return r;
+}
+__device__ __forceinline__ u64 mul(u64 a, u64 b) { return reduce128(mul_wide_native(a, b)); }
+__device__ __forceinline__ u64 sqr(u64 a) { return reduce128(mul_wide_native(a, a)); }
 // a*b + c  (fused: the addend rides on the first partial product)
 __device__ __forceinline__ u64 mad(u64 a, u64 b, u64 c) { return reduce128(mad_wide(a, b, c)); }
 

@@ -7,6 +7,9 @@
 #include "ntt.cuh"
 #include "poseidon_kernels.cuh"
 
+#include <dlfcn.h>
+#include <nccl.h> // types and prototypes only: libnccl.so.2 is dlopen'ed by gl_mgpu_init (single-GPU users need no NCCL)
+
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
@@ -53,12 +56,12 @@ struct Ctx {
     bool ready = false;
     int device = -1;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     void *arena = nullptr;
     size_t arena_bytes = 0;
     size_t scratch_limit = (size_t)8 << 30;
     std::atomic<uint64_t> launches{0};
-    float ms[3] = {0, 0, 0};
+    float ms[4] = {0, 0, 0, 0}; // LDE, leaf hashing, tree levels, multi-GPU exchange
     std::mutex mu;
 } g;
 
@@ -261,7 +264,7 @@ int merkletree_dev(u64 *tree, const u64 *src, u64 ncols, u64 nrows, bool timed)
 {
     if (nrows == 0) return GL_OK; // poseidon_goldilocks.cpp:268-271
     if (timed) CU(cudaEventRecord(g.ev[1], g.stream));
-    poseidon::launch_linear_hash_rows(tree, src, nrows, ncols, ncols, g.stream);
+    poseidon::launch_linear_hash_rows(tree, src, nrows, ncols, g.stream);
     g.launches++;
     CU(cudaGetLastError());
     if (timed) CU(cudaEventRecord(g.ev[2], g.stream));
@@ -281,6 +284,7 @@ int collect_timings(bool lde, bool tree)
     } else {
         g.ms[1] = g.ms[2] = 0;
     }
+    g.ms[3] = 0;
     return GL_OK;
 }
 
@@ -327,6 +331,88 @@ __global__ void k_fill_synthetic(u64 *dst, u64 n, u64 seed, u64 first)
     u64 stride = (u64)gridDim.x * blockDim.x;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         u64 z = seed + (first + i) * 0x9E3779B97F4A7C15ULL;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+        z = z ^ (z >> 31);
+        dst[i] = gl::canon(z);
+    }
+}
+
+// ---- multi-GPU: column-split LDE -> all-to-all to row blocks -> per-GPU subtrees -> gathered root
+struct Nccl {
+    void *h = nullptr;
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclSend) Send = nullptr;
+    decltype(&ncclRecv) Recv = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
+    u64 *top = nullptr; // (2*world-1)*4 words: gathered subtree roots + the levels above them
+} nc;
+
+#define NC(call)                                                                                                 \
+    do {                                                                                                         \
+        ncclResult_t r__ = (call);                                                                               \
+        if (r__ != ncclSuccess)                                                                                  \
+            return fail(GL_ERR_NCCL, "%s: %s (%s:%d)", #call, nc.GetErrorString ? nc.GetErrorString(r__) : "?", __FILE__, __LINE__); \
+    } while (0)
+
+int nccl_load()
+{
+    if (nc.h) return GL_OK;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *n : names)
+        if ((nc.h = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+    if (!nc.h) return fail(GL_ERR_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+#define SYM(field, name)                                                              \
+    nc.field = (decltype(nc.field))dlsym(nc.h, name);                                 \
+    if (!nc.field) return fail(GL_ERR_NCCL, "libnccl lacks %s", name)
+    SYM(GetUniqueId, "ncclGetUniqueId");
+    SYM(CommInitRank, "ncclCommInitRank");
+    SYM(CommDestroy, "ncclCommDestroy");
+    SYM(GetErrorString, "ncclGetErrorString");
+    SYM(GroupStart, "ncclGroupStart");
+    SYM(GroupEnd, "ncclGroupEnd");
+    SYM(Send, "ncclSend");
+    SYM(Recv, "ncclRecv");
+    SYM(AllGather, "ncclAllGather");
+#undef SYM
+    return GL_OK;
+}
+
+// first column of rank r when ncols columns are split over `world` ranks (balanced, contiguous)
+u64 col_start(u64 ncols, int world, int r) { return ncols * (u64)r / (u64)world; }
+
+// word offset of level l (0 = leaves) in a tree over h leaves (merklehash_goldilocks.hpp:25-28 layout)
+u64 level_offset(u64 h, u32 l)
+{
+    u64 off = 0;
+    for (u32 q = 0; q < l; q++) off += (h >> q) * 4;
+    return off;
+}
+
+// gather the `world` subtree roots and hash the log2(world) levels above them; result root on host
+int mgpu_top(const u64 *subtree_root, uint64_t root[4])
+{
+    NC(nc.AllGather(subtree_root, nc.top, 4, ncclUint64, nc.comm, g.stream));
+    g.launches += poseidon::launch_tree_levels(nc.top, (u64)nc.world, g.stream);
+    CU(cudaGetLastError());
+    if (root) CU(cudaMemcpyAsync(root, nc.top + gl_tree_num_elements(nc.world) - 4, 32, cudaMemcpyDeviceToHost, g.stream));
+    return GL_OK;
+}
+
+// Synthetic input restricted to a column range: dst[r*w + c] = word (r*ncols_total + col0 + c) of gl_fill_synthetic_dev.
+__global__ void k_fill_synthetic_cols(u64 *dst, u64 nrows, u64 col0, u64 w, u64 ncols_total, u64 seed)
+{
+    u64 stride = (u64)gridDim.x * blockDim.x, n = nrows * w;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        u64 r = i / w, c = i - r * w;
+        u64 z = seed + (r * ncols_total + col0 + c) * 0x9E3779B97F4A7C15ULL;
         z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
         z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
         z = z ^ (z >> 31);
@@ -537,7 +623,7 @@ int gl_hash_full_result_dev(uint64_t *out, const uint64_t *in, uint64_t n)
 int gl_linear_hash_rows_dev(uint64_t *out, const uint64_t *src, uint64_t ncols, uint64_t nrows)
 {
     TRY(need_ctx());
-    poseidon::launch_linear_hash_rows((u64 *)out, (const u64 *)src, nrows, ncols, ncols, g.stream);
+    poseidon::launch_linear_hash_rows((u64 *)out, (const u64 *)src, nrows, ncols, g.stream);
     if (nrows) g.launches++;
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(g.stream));
@@ -643,6 +729,138 @@ int gl_fill_synthetic_dev(uint64_t *dst, uint64_t words, uint64_t seed, uint64_t
     g.launches++;
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+// ---- multi-GPU (one process per GPU) ----------------------------------------------------
+int gl_mgpu_unique_id(uint8_t id[128])
+{
+    TRY(nccl_load());
+    ncclUniqueId u;
+    NC(nc.GetUniqueId(&u));
+    static_assert(sizeof(u) == 128, "ncclUniqueId size");
+    memcpy(id, &u, 128);
+    return GL_OK;
+}
+
+int gl_mgpu_init(const uint8_t id[128], int rank, int world)
+{
+    TRY(need_ctx());
+    TRY(nccl_load());
+    if (nc.comm) return fail(GL_ERR_ARG, "multi-GPU communicator already initialised");
+    if (world < 1 || world > poseidon::kMaxPanels || (world & (world - 1)) || rank < 0 || rank >= world)
+        return fail(GL_ERR_ARG, "world size %d (rank %d): need a power of two <= %d", world, rank, poseidon::kMaxPanels);
+    ncclUniqueId u;
+    memcpy(&u, id, 128);
+    NC(nc.CommInitRank(&nc.comm, world, u, rank));
+    nc.rank = rank;
+    nc.world = world;
+    CU(cudaMalloc(&nc.top, gl_tree_num_elements(world) * 8));
+    return GL_OK;
+}
+
+int gl_mgpu_shutdown(void)
+{
+    if (nc.comm) {
+        cudaStreamSynchronize(g.stream);
+        nc.CommDestroy(nc.comm);
+        nc.comm = nullptr;
+    }
+    if (nc.top) cudaFree(nc.top);
+    nc.top = nullptr;
+    nc.rank = 0;
+    nc.world = 1;
+    return GL_OK;
+}
+
+uint64_t gl_mgpu_col_start(uint64_t ncols, int world, int rank) { return col_start(ncols, world, rank); }
+
+int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, const uint64_t *in_cols, uint64_t n_ext,
+                   uint64_t n, uint64_t ncols_total, uint64_t root[4])
+{
+    TRY(need_ctx());
+    if (!nc.comm) return fail(GL_ERR_ARG, "gl_commit_mgpu: call gl_mgpu_init first");
+    const int G = nc.world, me = nc.rank;
+    if (n == 0 || n_ext == 0 || !is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "commit: bad domain %llu -> %llu", (u64)n, (u64)n_ext);
+    if (n_ext < (u64)G) return fail(GL_ERR_ARG, "commit: %llu extended rows cannot be split over %d ranks", (u64)n_ext, G);
+    const u64 rows = n_ext / G;
+    const u64 c0 = col_start(ncols_total, G, me), w = col_start(ncols_total, G, me + 1) - c0;
+
+    CU(cudaEventRecord(g.ev[0], g.stream));
+    TRY(extend_pol_dev((u64 *)lde_cols, (const u64 *)in_cols, n_ext, n, w));
+    CU(cudaEventRecord(g.ev[4], g.stream));
+
+    // all-to-all: rows [h*rows, (h+1)*rows) of my column block go to rank h; I receive rank p's columns of my rows
+    poseidon::RowPanels rp = {};
+    rp.npanels = (u32)G;
+    for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
+    for (int p = 0; p < G; p++) rp.base[p] = (const u64 *)row_panels + rows * rp.start[p];
+    NC(nc.GroupStart());
+    for (int p = 0; p < G; p++) {
+        if (p == me) continue;
+        const u64 wp = rp.start[p + 1] - rp.start[p];
+        if (w) NC(nc.Send((const u64 *)lde_cols + (u64)p * rows * w, rows * w, ncclUint64, p, nc.comm, g.stream));
+        if (wp) NC(nc.Recv((void *)rp.base[p], rows * wp, ncclUint64, p, nc.comm, g.stream));
+    }
+    NC(nc.GroupEnd());
+    if (w) CU(cudaMemcpyAsync((void *)rp.base[me], (const u64 *)lde_cols + (u64)me * rows * w, rows * w * 8, cudaMemcpyDeviceToDevice, g.stream));
+    CU(cudaEventRecord(g.ev[1], g.stream));
+
+    poseidon::launch_linear_hash_panels((u64 *)subtree, rp, rows, g.stream);
+    g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(g.ev[2], g.stream));
+    g.launches += poseidon::launch_tree_levels((u64 *)subtree, rows, g.stream);
+    CU(cudaGetLastError());
+    TRY(mgpu_top((const u64 *)subtree + gl_tree_num_elements(rows) - 4, root));
+    CU(cudaEventRecord(g.ev[3], g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    CU(cudaEventElapsedTime(&g.ms[0], g.ev[0], g.ev[4]));
+    CU(cudaEventElapsedTime(&g.ms[3], g.ev[4], g.ev[1]));
+    CU(cudaEventElapsedTime(&g.ms[1], g.ev[1], g.ev[2]));
+    CU(cudaEventElapsedTime(&g.ms[2], g.ev[2], g.ev[3]));
+    return GL_OK;
+}
+
+int gl_mgpu_gather_tree(uint64_t *tree_full, const uint64_t *subtree, uint64_t n_ext)
+{
+    TRY(need_ctx());
+    if (!nc.comm) return fail(GL_ERR_ARG, "gl_mgpu_gather_tree: call gl_mgpu_init first");
+    const u64 G = (u64)nc.world, rows = n_ext / G;
+    u32 lv = 0;
+    for (u64 cnt = rows; cnt >= 1; cnt >>= 1, lv++) {
+        NC(nc.AllGather((const u64 *)subtree + level_offset(rows, lv), (u64 *)tree_full + level_offset(n_ext, lv), cnt * 4, ncclUint64,
+                        nc.comm, g.stream));
+        if (cnt == 1) break;
+    }
+    // levels above the subtree roots (G nodes at level lv)
+    u64 pending = G, next_index = level_offset(n_ext, lv);
+    while (pending > 1) {
+        poseidon::k_tree_level<<<poseidon::grid_for(pending / 2), poseidon::kThreads, 0, g.stream>>>((u64 *)tree_full + next_index + pending * 4,
+                                                                                                       (u64 *)tree_full + next_index, pending / 2);
+        g.launches++;
+        next_index += pending * 4;
+        pending /= 2;
+    }
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_fill_synthetic_cols_dev(uint64_t *dst, uint64_t nrows, uint64_t col0, uint64_t ncols_local, uint64_t ncols_total, uint64_t seed)
+{
+    TRY(need_ctx());
+    if (nrows == 0 || ncols_local == 0) return GL_OK;
+    k_fill_synthetic_cols<<<148 * 8, 256, 0, g.stream>>>((u64 *)dst, nrows, col0, ncols_local, ncols_total, seed);
+    g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_last_timings4(float ms[4])
+{
+    for (int i = 0; i < 4; i++) ms[i] = g.ms[i];
     return GL_OK;
 }
 

@@ -23,35 +23,55 @@ __global__ void __launch_bounds__(kThreads) k_hash_full_result(u64 *__restrict__
     for (int i = 0; i < 12; i++) out[idx * 12 + i] = gl::canon(s[i]);
 }
 
-// One thread per row.  Row r starts at src + r*pitch and has ncols words (pitch in words).
+// Where the words of a row live.  Single GPU: one panel = the row-major matrix.  Multi-GPU (after the
+// column-split -> row-block exchange): panel g holds columns [start[g], start[g+1]) of this
+// rank's rows, row-major with pitch start[g+1]-start[g], as received from rank g.
+constexpr int kMaxPanels = 8;
+struct RowPanels {
+    const u64 *base[kMaxPanels];
+    u32 start[kMaxPanels + 1];
+    u32 npanels;
+};
+
+template <bool PANELS>
+__device__ __forceinline__ u64 row_word(const RowPanels &rp, const u64 *p0, u64 row, u32 col)
+{
+    if (!PANELS) return p0[col];
+    u32 g = 0;
+    while (g + 1 < rp.npanels && col >= rp.start[g + 1]) g++; // warp-uniform
+    const u32 w = rp.start[g + 1] - rp.start[g];
+    return rp.base[g][row * w + (col - rp.start[g])];
+}
+
+// One thread per row (PoseidonGoldilocks::linear_hash, poseidon_goldilocks.cpp:229-265).
 // ncols <= 4: the row is returned zero-padded WITHOUT hashing (reference :234-239).
-__global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__ digests, const u64 *__restrict__ src,
-                                                               u64 nrows, u64 ncols, u64 pitch)
+template <bool PANELS>
+__global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__ digests, const RowPanels rp, u64 nrows, u32 ncols)
 {
     u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nrows) return;
-    const u64 *p = src + row * pitch;
+    const u64 *p = PANELS ? nullptr : rp.base[0] + row * ncols;
     u64 *d = digests + row * 4;
     if (ncols <= 4) {
 #pragma unroll
-        for (int i = 0; i < 4; i++) d[i] = (u64)i < ncols ? gl::canon(p[i]) : 0;
+        for (u32 i = 0; i < 4; i++) d[i] = i < ncols ? gl::canon(row_word<PANELS>(rp, p, row, i)) : 0;
         return;
     }
     u64 s[12];
 #pragma unroll
     for (int i = 8; i < 12; i++) s[i] = 0;
-    u64 full = ncols >> 3;
-    for (u64 c = 0; c < full; c++) {
+    const u32 full = ncols >> 3;
+    for (u32 c = 0; c < full; c++) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) s[i] = p[c * 8 + i];
+        for (u32 i = 0; i < 8; i++) s[i] = row_word<PANELS>(rp, p, row, c * 8 + i);
         permute(s);
 #pragma unroll
         for (int i = 0; i < 4; i++) s[8 + i] = s[i];
     }
-    u32 rem = (u32)(ncols & 7);
+    const u32 rem = ncols & 7;
     if (rem) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) s[i] = (u32)i < rem ? p[full * 8 + i] : 0;
+        for (u32 i = 0; i < 8; i++) s[i] = i < rem ? row_word<PANELS>(rp, p, row, full * 8 + i) : 0;
         permute(s);
     }
 #pragma unroll
@@ -112,9 +132,19 @@ inline void launch_hash_full_result(u64 *out, const u64 *in, u64 n, cudaStream_t
     if (n) k_hash_full_result<<<grid_for(n), kThreads, 0, st>>>(out, in, n);
 }
 
-inline void launch_linear_hash_rows(u64 *digests, const u64 *src, u64 nrows, u64 ncols, u64 pitch, cudaStream_t st)
+inline void launch_linear_hash_rows(u64 *digests, const u64 *src, u64 nrows, u64 ncols, cudaStream_t st)
 {
-    if (nrows) k_linear_hash_rows<<<grid_for(nrows), kThreads, 0, st>>>(digests, src, nrows, ncols, pitch);
+    if (!nrows) return;
+    RowPanels rp = {};
+    rp.base[0] = src;
+    rp.start[1] = (u32)ncols;
+    rp.npanels = 1;
+    k_linear_hash_rows<false><<<grid_for(nrows), kThreads, 0, st>>>(digests, rp, nrows, (u32)ncols);
+}
+
+inline void launch_linear_hash_panels(u64 *digests, const RowPanels &rp, u64 nrows, cudaStream_t st)
+{
+    if (nrows) k_linear_hash_rows<true><<<grid_for(nrows), kThreads, 0, st>>>(digests, rp, nrows, rp.start[rp.npanels]);
 }
 
 // Levels above the leaves.  tree holds (2*nrows-1)*4 words, leaves first (merklehash_goldilocks.hpp:25-28).

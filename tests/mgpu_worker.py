@@ -1,0 +1,115 @@
+"""Worker of the multi-rank tests (launched with torch.distributed.run by test_shard_plan.py / test_gpu_mgpu.py).
+
+  mode "gloo": CPU only.  Every rank runs the ORACLE on its column block, the exchange goes through
+               torch.distributed (gloo send/recv), the shard plan (merlin-zkevm-prover_b200/shard_plan.py)
+               assembles the tree; checked against the single-process oracle.  Tests the host-side logic.
+  mode "nccl": one GPU per rank.  gl_commit_mgpu / gl_mgpu_gather_tree through the C ABI, checked against the oracle.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as ge  # noqa: E402
+from oracle import pyoracle  # noqa: E402
+
+SHAPES = [(1 << 10, 1 << 11, 37), (1 << 8, 1 << 12, 9), (1 << 6, 1 << 7, 3), (1 << 9, 1 << 10, 64)]
+
+
+def top_levels(o, tree, n_ext, first_level, sp):
+    lv, cnt = first_level, n_ext >> first_level
+    while cnt >= 1:
+        src = tree[sp.level_offset(n_ext, lv - 1):sp.level_offset(n_ext, lv - 1) + cnt * 2 * 4].reshape(cnt, 8)
+        for i in range(cnt):
+            st = o.hash_full_result(np.concatenate([src[i], np.zeros(4, dtype=np.uint64)]))
+            tree[sp.level_offset(n_ext, lv) + 4 * i:sp.level_offset(n_ext, lv) + 4 * i + 4] = st[:4]
+        if cnt == 1:
+            break
+        cnt >>= 1
+        lv += 1
+    return tree
+
+
+def main():
+    mode = sys.argv[1]
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    glb = ge.load()
+    sp = __import__("importlib").import_module("merlin_zkevm_prover_b200.shard_plan")
+    o = pyoracle.oracle()
+    if mode == "gloo":
+        dist.init_process_group("gloo")
+    else:
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        glb.init(local_rank)
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(glb.mgpu_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        glb.mgpu_init(idt.cpu().numpy().tobytes(), rank, world)
+
+    for (n, e, ncols) in SHAPES:
+        x, _ = o.xorshift(n * ncols)
+        x = x.reshape(n, ncols)
+        lde_full = o.extend_pol(x, e)
+        tree_full = o.merkletree(lde_full)
+        c0, c1 = sp.col_range(ncols, world, rank)
+        r0, r1 = sp.row_range(e, world, rank)
+        rows = e // world
+        if mode == "gloo":
+            mine = o.extend_pol(np.ascontiguousarray(x[:, c0:c1]), e) if c1 > c0 else np.zeros((e, 0), dtype=np.uint64)
+            assert np.array_equal(mine, lde_full[:, c0:c1])
+            chunks = sp.send_chunks(mine, world)
+            panels = [None] * world
+            reqs = []
+            for p in range(world):
+                pc0, pc1 = sp.col_range(ncols, world, p)
+                if p == rank:
+                    panels[p] = chunks[p]
+                    continue
+                panels[p] = np.zeros((rows, pc1 - pc0), dtype=np.uint64)
+                if c1 > c0:
+                    reqs.append(dist.isend(torch.from_numpy(chunks[p].view(np.int64)), p))
+                if pc1 > pc0:
+                    reqs.append(dist.irecv(torch.from_numpy(panels[p].view(np.int64)), p))
+            for r in reqs:
+                r.wait()
+            myrows = sp.rows_from_panels(panels)
+            assert np.array_equal(myrows, lde_full[r0:r1])
+            sub = o.merkletree(myrows)
+            subs = [torch.zeros(sub.size, dtype=torch.int64) for _ in range(world)]
+            dist.all_gather(subs, torch.from_numpy(sub.view(np.int64)))
+            subs = [s.numpy().view(np.uint64) for s in subs]
+            tree, first = sp.assemble_tree(subs, e)
+            tree = top_levels(o, tree, e, first, sp) if world > 1 else tree
+            assert np.array_equal(tree, tree_full), "assembled tree differs (%d,%d,%d)" % (n, e, ncols)
+        else:
+            w = c1 - c0
+            din = glb.DeviceBuffer(max(1, n * w)).upload(np.ascontiguousarray(x[:, c0:c1]))
+            dlde = glb.DeviceBuffer(max(1, e * w))
+            dpan = glb.DeviceBuffer(max(1, rows * ncols))
+            dsub = glb.DeviceBuffer(glb.tree_num_elements(rows))
+            dfull = glb.DeviceBuffer(glb.tree_num_elements(e))
+            root = glb.commit_mgpu(dlde.ptr, dpan.ptr, dsub.ptr, din.ptr, e, n, ncols)
+            assert np.array_equal(root, tree_full[-4:]), "root differs (%d,%d,%d)" % (n, e, ncols)
+            assert np.array_equal(dlde.download(e * w).reshape(e, w), lde_full[:, c0:c1])
+            pan = dpan.download(rows * ncols)
+            for p, (off, pw) in enumerate(sp.panel_offsets(e, ncols, world)):
+                pc0 = sp.col_start(ncols, world, p)
+                assert np.array_equal(pan[off:off + rows * pw].reshape(rows, pw), lde_full[r0:r1, pc0:pc0 + pw])
+            glb.mgpu_gather_tree(dfull.ptr, dsub.ptr, e)
+            assert np.array_equal(dfull.download(), tree_full), "gathered tree differs"
+        dist.barrier()
+    if mode == "nccl":
+        glb.mgpu_shutdown()
+    dist.destroy_process_group()
+    print("mgpu_worker %s rank %d/%d ok" % (mode, rank, world))
+
+
+if __name__ == "__main__":
+    main()

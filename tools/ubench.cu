@@ -7,6 +7,7 @@
 #include "poseidon_kernels.cuh"
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 typedef unsigned long long u64;
@@ -37,6 +38,23 @@ __global__ void k_issue(u64 *out, int iters, u32 seed)
                 }
                 if (OP == 5) asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(r[i]) : "r"(b));
                 if (OP == 6) asm volatile("shf.l.wrap.b32 %0, %0, %1, 7;" : "+r"(r[i]) : "r"(s[i]));
+                if (OP == 8) { // 1 wide mad + 2 independent LOP3
+                    asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a), "r"(b));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(r[i]) : "r"(a), "r"(b));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(s[i]) : "r"(a), "r"(b));
+                }
+                if (OP == 9) { // 1 wide mad + 1 LOP3
+                    asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a), "r"(b));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(r[i]) : "r"(a), "r"(b));
+                }
+                if (OP == 10) { // 1 wide mad + 1 plain IADD3 (no carry)
+                    asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a), "r"(b));
+                    asm volatile("add.u32 %0, %0, %1;" : "+r"(r[i]) : "r"(b));
+                }
+                if (OP == 11) { // 2 plain IADD3
+                    asm volatile("add.u32 %0, %0, %1;" : "+r"(r[i]) : "r"(b));
+                    asm volatile("add.u32 %0, %0, %1;" : "+r"(s[i]) : "r"(a));
+                }
                 if (OP == 7) { // mad.lo.cc + madc.hi.cc pair (expected: one IMAD.WIDE with carry) + addc
                     asm volatile("mad.lo.cc.u32 %0, %3, %4, %0;\n\tmadc.hi.cc.u32 %1, %3, %4, %1;\n\taddc.u32 %2, %2, 0;"
                                  : "+r"(r[i]), "+r"(s[i]), "+r"(a) : "r"(b), "r"(seed));
@@ -121,11 +139,22 @@ int main(int argc, char **argv)
     u64 *out;
     CK(cudaMalloc(&out, (size_t)sms * 16 * 1024 * 8));
 
+    const bool only_perm = argc > 1 && !strcmp(argv[1], "perm");
+    if (only_perm) {
+        k_perm<<<sms * 8, 128>>>(out, 40, 0x1234567ULL);
+        CK(cudaDeviceSynchronize());
+        k_perm<<<sms * 8, 128>>>(out, 40, 0x1234567ULL);
+        CK(cudaDeviceSynchronize());
+        printf("perm only done\n");
+        return 0;
+    }
+    const bool skip_mem = argc > 1 && !strcmp(argv[1], "nomem");
     // ---- 1. issue rates
     const char *names[] = {"IMAD.WIDE.U32 (mad.wide.u32)", "IMAD (mad.lo.u32)", "IADD3+IADD3.X pair (add.cc/addc)", "LOP3", "mix: 1 mad.wide + 1 add.cc/addc pair",
-                           "IMAD.HI (mul.hi.u32)", "SHF", "mad.lo.cc+madc.hi.cc+addc"};
-    const int ops_per[] = {1, 1, 2, 1, 3, 1, 1, 3};
-    for (int op = 0; op < 8; op++) {
+                           "IMAD.HI (mul.hi.u32)", "SHF", "mad.lo.cc+madc.hi.cc+addc",
+                           "mix: 1 mad.wide + 2 LOP3", "mix: 1 mad.wide + 1 LOP3", "mix: 1 mad.wide + 1 IADD", "2 IADD (no carry)"};
+    const int ops_per[] = {1, 1, 2, 1, 3, 1, 1, 3, 3, 2, 2, 2};
+    for (int op = 0; op < 12; op++) {
         for (int warps = 8; warps <= 32; warps *= 2) {
             int blocks = sms * 2, threads = warps * 32 / 2, iters = 2000;
             for (int rep = 0; rep < 2; rep++) {
@@ -139,6 +168,10 @@ int main(int argc, char **argv)
                 case 5: k_issue<5><<<blocks, threads>>>(out, iters, 12345); break;
                 case 6: k_issue<6><<<blocks, threads>>>(out, iters, 12345); break;
                 case 7: k_issue<7><<<blocks, threads>>>(out, iters, 12345); break;
+                case 8: k_issue<8><<<blocks, threads>>>(out, iters, 12345); break;
+                case 9: k_issue<9><<<blocks, threads>>>(out, iters, 12345); break;
+                case 10: k_issue<10><<<blocks, threads>>>(out, iters, 12345); break;
+                case 11: k_issue<11><<<blocks, threads>>>(out, iters, 12345); break;
                 }
                 CK(cudaEventRecord(e1));
                 CK(cudaEventSynchronize(e1));
@@ -182,7 +215,7 @@ int main(int argc, char **argv)
         printf("perm   warps/SM=%2d  %8.3f ms  %8.2f M perm/s\n", bps * 4, ms, (double)blocks * threads * iters / ms / 1e3);
     }
     // ---- 3. row-segment bandwidth
-    {
+    if (!skip_mem) {
         const u64 pitch = 600, rows = 1ULL << 22; // 20 GB matrix
         u64 *a, *b;
         size_t bytes = rows * pitch * 8;
