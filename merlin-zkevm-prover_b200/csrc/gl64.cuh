@@ -45,7 +45,9 @@ __device__ __forceinline__ void madw(u64 &acc, u32 a, u32 b)
 
 __device__ __forceinline__ u64 pack(u32 lo, u32 hi) { return ((u64)hi << 32) | lo; }
 
-__device__ __forceinline__ u64 canon(u64 x) { return x >= P ? x - P : x; }
+// x mod p for x < 2^64: x >= p  <=>  x + (2^32-1) carries out of 64 bits, and then x - p = x + (2^32-1) - 2^64.
+// Written so that ptxas emits IADD3, IADD3.X, SEL, IMAD.WIDE (4 instructions; the compare form needs 6).
+__device__ __forceinline__ u64 canon_slow(u64 x) { return x >= P ? x - P : x; }
 
 // 64x64 -> 128, even/odd column scheme: 4 wide multiplies, one carry chain.
 __device__ __forceinline__ u128 mul_wide(u64 a, u64 b)
@@ -124,7 +126,7 @@ __device__ __forceinline__ u64 reduce128(u128 x)
     return pack(r0, r1);
 }
 
-// 96-bit input (x3 == 0): {x0,x1} + x2*(2^32-1); one carry correction.
+// 96-bit input (x3 == 0): {x0,x1} + x2*(2^32-1), then + carry*(2^32-1) (cannot carry again): 2 IMAD.WIDE + SEL.
 __device__ __forceinline__ u64 reduce96(u32 x0, u32 x1, u32 x2)
 {
     u32 r0, r1;
@@ -133,9 +135,8 @@ __device__ __forceinline__ u64 reduce96(u32 x0, u32 x1, u32 x2)
         "mad.lo.cc.u32 %0, %4, %5, %2;\n\t"
         "madc.hi.cc.u32 %1, %4, %5, %3;\n\t"
         "addc.u32 k, 0, 0;\n\t"
-        "neg.s32 k, k;\n\t"                          // 0 or 0xFFFFFFFF
-        "add.cc.u32 %0, %0, k;\n\t"
-        "addc.u32 %1, %1, 0;\n\t"
+        "mad.lo.cc.u32 %0, k, %5, %0;\n\t"
+        "madc.hi.u32 %1, k, %5, %1;\n\t"
         "}"
         : "=&r"(r0), "=&r"(r1)
         : "r"(x0), "r"(x1), "r"(x2), "r"(c_eps[0]));
@@ -227,7 +228,8 @@ __device__ __forceinline__ u64 add(u64 a, u64 b)
     return pack(r0, r1);
 }
 
-// a + b where b is CANONICAL (< p): a single wrap suffices.
+// a + b where b is CANONICAL (< p): the 65-bit sum folds with one IMAD.WIDE, s + carry*(2^32-1)
+// (a + b - 2^64 + 2^32 - 1 < 2^64 because b < p).  IADD3, IADD3.X, SEL, IMAD.WIDE.
 __device__ __forceinline__ u64 add_c(u64 a, u64 b)
 {
     u32 r0, r1;
@@ -236,13 +238,43 @@ __device__ __forceinline__ u64 add_c(u64 a, u64 b)
         "add.cc.u32 %0, %2, %4;\n\t"
         "addc.cc.u32 %1, %3, %5;\n\t"
         "addc.u32 k, 0, 0;\n\t"
-        "neg.s32 k, k;\n\t"
-        "add.cc.u32 %0, %0, k;\n\t"
-        "addc.u32 %1, %1, 0;\n\t"
+        "mad.lo.cc.u32 %0, k, %6, %0;\n\t"
+        "madc.hi.u32 %1, k, %6, %1;\n\t"
         "}"
         : "=&r"(r0), "=&r"(r1)
-        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)), "r"(c_eps[0]));
     return pack(r0, r1);
+}
+
+__device__ __forceinline__ u64 canon(u64 x)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 t0, t1, k;\n\t"
+        "add.cc.u32 t0, %2, %4;\n\t"
+        "addc.cc.u32 t1, %3, 0;\n\t"
+        "addc.u32 k, 0, 0;\n\t"
+        "mad.lo.cc.u32 %0, k, %4, %2;\n\t"
+        "madc.hi.u32 %1, k, %4, %3;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)x), "r"((u32)(x >> 32)), "r"(c_eps[0]));
+    return pack(r0, r1);
+}
+
+// x * 2^S mod p for a compile-time 0 <= S < 96 (2^96 = -1): funnel shifts + one short reduction.
+template <int S>
+__device__ __forceinline__ u64 mul_pow2(u64 x)
+{
+    static_assert(S >= 0 && S < 96, "shift out of range");
+    constexpr int r = S % 32, q = S / 32;
+    const u32 x0 = (u32)x, x1 = (u32)(x >> 32);
+    u32 y0, y1, y2;
+    if (r == 0) { y0 = x0; y1 = x1; y2 = 0; }
+    else { y0 = x0 << r; y1 = __funnelshift_l(x0, x1, r); y2 = x1 >> (32 - r); }
+    if (q == 0) return reduce96(y0, y1, y2);
+    if (q == 1) { u128 v; v.x0 = 0; v.x1 = y0; v.x2 = y1; v.x3 = y2; return reduce128(v); }
+    return reduce160(0, 0, y0, y1, y2);
 }
 
 // a - b where b is CANONICAL (< p): a single wrap suffices.

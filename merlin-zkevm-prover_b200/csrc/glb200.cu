@@ -59,6 +59,8 @@ struct Ctx {
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     void *arena = nullptr;
     size_t arena_bytes = 0;
+    u64 *roots = nullptr, *rscale = nullptr; // twiddle / coset-scale tables (device)
+    u32 log_roots = 0, log_rscale = 0;
     size_t scratch_limit = (size_t)8 << 30;
     std::atomic<uint64_t> launches{0};
     float ms[4] = {0, 0, 0, 0}; // LDE, leaf hashing, tree levels, multi-GPU exchange
@@ -138,19 +140,59 @@ u32 ilog2(u64 n)
 
 bool is_pow2(u64 n) { return n && !(n & (n - 1)); }
 
-// ---- NTT plan / launch ---------------------------------------------------------------------------
-template <int B2, bool INV>
+// ---- NTT tables / plan / launch ---------------------------------------------------------------------
+// roots[i] = w_(2^L)^i for the largest transform seen so far (the reference keeps the same table per
+// NTT_Goldilocks object and REBUILDS it serially on every extendPol, ntt_goldilocks.cpp:328; here it is
+// built once on the device and reused); rscale[i] = 7^i / n for the most recent extend size (computeR,
+// ntt_goldilocks.hpp:153-165).
+constexpr u32 kMaxLogRoots = 27;
+
+int ensure_roots(u32 logn)
+{
+    if (logn > kMaxLogRoots) return fail(GL_ERR_NOMEM, "NTT of size 2^%u needs a %llu MiB twiddle table; this build caps it at 2^%u", logn, (8ULL << logn) >> 20, kMaxLogRoots);
+    if (g.roots && g.log_roots >= logn) return GL_OK;
+    u32 L = logn < 16 ? 16 : logn;
+    if (g.roots) {
+        CU(cudaStreamSynchronize(g.stream));
+        CU(cudaFree(g.roots));
+        g.roots = nullptr;
+    }
+    CU(cudaMalloc(&g.roots, (size_t)8 << L));
+    ntt::k_build_roots<<<148 * 4, 256, 0, g.stream>>>(g.roots, L);
+    g.launches++;
+    CU(cudaGetLastError());
+    g.log_roots = L;
+    return GL_OK;
+}
+
+int ensure_rscale(u32 logn)
+{
+    if (g.rscale && g.log_rscale == logn) return GL_OK;
+    if (g.rscale) {
+        CU(cudaStreamSynchronize(g.stream));
+        CU(cudaFree(g.rscale));
+        g.rscale = nullptr;
+    }
+    CU(cudaMalloc(&g.rscale, (size_t)8 << logn));
+    ntt::k_build_rscale<<<148 * 4, 256, 0, g.stream>>>(g.rscale, logn);
+    g.launches++;
+    CU(cudaGetLastError());
+    g.log_rscale = logn;
+    return GL_OK;
+}
+
+template <int B2, bool LAST>
 int launch_pass_t(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
 {
     constexpr int R = 16 << B2;
-    size_t smem = (B2 > 0 ? (size_t)R * ntt::kTileCols * 8 : 0) + (size_t)R * 8 + 32 * 8;
+    size_t smem = B2 > 0 ? (size_t)R * ntt::kTileCols * 8 : 0;
     static bool attr_done = false;
-    if (!attr_done) {
-        CU(cudaFuncSetAttribute(ntt::k_pass<B2, INV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (!attr_done && smem > 48 * 1024) {
+        CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_done = true;
     }
     dim3 grid((unsigned)ntiles, coltiles), block(32, 1 << B2);
-    ntt::k_pass<B2, INV><<<grid, block, smem, g.stream>>>(p);
+    ntt::k_pass<B2, LAST><<<grid, block, smem, g.stream>>>(p);
     g.launches++;
     CU(cudaGetLastError());
     return GL_OK;
@@ -162,7 +204,8 @@ int launch_pass(const ntt::PassParams &p)
     u64 ntiles = (1ULL << p.logn) >> b;
     u32 coltiles = (p.ncols + ntt::kTileCols - 1) / ntt::kTileCols;
     if (ntiles > 0x7FFFFFFFULL || coltiles > 65535) return fail(GL_ERR_ARG, "grid too large");
-    switch ((b - 4) * 2 + (p.inverse ? 1 : 0)) {
+    const bool last = p.pass + 1 == p.npass;
+    switch ((b - 4) * 2 + (last ? 1 : 0)) {
     case 0: return launch_pass_t<0, false>(p, ntiles, coltiles);
     case 1: return launch_pass_t<0, true>(p, ntiles, coltiles);
     case 2: return launch_pass_t<1, false>(p, ntiles, coltiles);
@@ -198,6 +241,12 @@ int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpit
     u32 m = (logn + 7) / 8;
     p.npass = m;
     for (u32 i = 0; i < m; i++) p.bits[i] = logn / m + (i < logn % m ? 1 : 0);
+    if (m > 1) TRY(ensure_roots(logn));
+    if (scale_mode == 2) TRY(ensure_rscale(logn));
+    p.roots = g.roots;
+    p.log_roots = g.log_roots;
+    p.rscale = g.rscale;
+    p.cscale = scale_mode == 1 ? hpow((P + 1) / 2, logn) : 0; // 2^-logn
     u32 prev = 0;
     for (u32 i = 0; i < m; i++) {
         p.pass = i;
@@ -472,6 +521,10 @@ void gl_shutdown(void)
     if (g.arena) cudaFree(g.arena);
     g.arena = nullptr;
     g.arena_bytes = 0;
+    if (g.roots) cudaFree(g.roots);
+    if (g.rscale) cudaFree(g.rscale);
+    g.roots = g.rscale = nullptr;
+    g.log_roots = g.log_rscale = 0;
     for (auto &e : g.ev) { cudaEventDestroy(e); e = nullptr; }
     cudaStreamDestroy(g.stream);
     g.stream = nullptr;

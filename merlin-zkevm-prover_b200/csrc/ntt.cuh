@@ -64,9 +64,28 @@ __host__ __device__ constexpr int bitrev(int x, int bits)
     return r;
 }
 
-// In-register DFT of size 2^LOG on x[0 .. 2^LOG): decimation in frequency, so that on return
-// register i holds output index bitrev(i).  Twiddles are powers of two: w_(2^LOG) = 2^(192/2^LOG).
-template <int LOG, bool INV>
+// d * 2^sh for the shifts that occur inside radix-16/8/4 butterflies (multiples of 12 below 96).  `sh` is a
+// compile-time constant after unrolling; the switch folds away.
+__device__ __forceinline__ u64 mul_pow2_sel(u64 d, int sh)
+{
+    switch (sh) {
+    case 12: return gl::mul_pow2<12>(d);
+    case 24: return gl::mul_pow2<24>(d);
+    case 36: return gl::mul_pow2<36>(d);
+    case 48: return gl::mul_pow2<48>(d);
+    case 60: return gl::mul_pow2<60>(d);
+    case 72: return gl::mul_pow2<72>(d);
+    case 84: return gl::mul_pow2<84>(d);
+    default: return d;
+    }
+}
+
+// In-register forward DFT of size 2^LOG on x[0 .. 2^LOG): decimation in frequency, so that on return
+// register i holds output index bitrev(i).  Twiddles are powers of two: w_(2^LOG) = 2^(192/2^LOG)
+// (Goldilocks::W[1..6] = 2^96, 2^48, 2^24, 2^12, 2^6, 2^3; goldilocks_base_field.cpp:11-18), so a butterfly
+// is canon (4) + add (4) + sub (5) instructions and, for 17 of the 32 butterflies of a radix-16, a
+// 6-8 instruction shift-multiply.  Values stay lazily reduced; only the subtrahend is canonicalised.
+template <int LOG>
 __device__ __forceinline__ void dft_regs(u64 *x)
 {
     constexpr int N = 1 << LOG;
@@ -78,15 +97,10 @@ __device__ __forceinline__ void dft_regs(u64 *x)
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int ia = blk * 2 * half + i, ib = ia + half;
-                u64 a = x[ia], b = gl::canon(x[ib]);
+                const u64 a = x[ia], b = gl::canon(x[ib]);
                 x[ia] = gl::add_c(a, b);
-                u64 d = gl::sub_c(a, b);
-                const int e = i << s;               // exponent of w_N, 0 <= e < N/2
-                if (e != 0) {
-                    const int sh = (192 / N) * (INV ? (N - e) : e);
-                    d = gl::mul(d, pow2mod(sh));
-                }
-                x[ib] = d;
+                const u64 d = gl::sub_c(a, b);
+                x[ib] = mul_pow2_sel(d, (192 / N) * (i << s)); // exponent of w_N: i << s < N/2
             }
         }
     }
@@ -102,119 +116,85 @@ struct PassParams {
     u32 bits[4];        // bits per pass
     u32 log_rest;       // sum of bits of later passes
     u32 log_prev;       // sum of bits of earlier passes
-    int inverse;        // use w^-1
+    int inverse;        // last pass: output k goes to row (n-k) mod n (INTT = forward NTT + index reversal,
+                        // exactly as the reference does it, ntt_goldilocks.cpp:139-148); k_tiny: use w^-1
     int scale_mode;     // last pass only: 0 none, 1 multiply by 1/n, 2 multiply row i by 7^i / n
     u64 nvalid;         // source rows >= nvalid are read as zeros (zero-padded LDE input)
+    const u64 *roots;   // roots[i] = w_(2^log_roots)^i, i < 2^log_roots  (inter-pass twiddles)
+    u32 log_roots;
+    const u64 *rscale;  // scale_mode 2: rscale[i] = 7^i / n, i < n
+    u64 cscale;         // scale_mode 1: 1/n
 };
 
 template <int B2> struct Step2 {
-    template <bool INV> static __device__ __forceinline__ void run(u64 *y)
+    static __device__ __forceinline__ void run(u64 *y)
     {
         constexpr int R2 = 1 << B2;
 #pragma unroll
-        for (int g = 0; g < 16 / R2; g++) dft_regs<B2, INV>(y + g * R2);
+        for (int g = 0; g < 16 / R2; g++) dft_regs<B2>(y + g * R2);
     }
 };
 
-// B2 = log2(R) - 4, blockDim = (32, 2^B2).
-template <int B2, bool INV>
-__global__ void __launch_bounds__(32 << B2) k_pass(PassParams p)
+// One pass: a radix-R DFT (R = 16 * 2^B2) along one mixed-radix digit of the row index, on a tile of
+// R rows x 32 columns.  blockDim = (32, 2^B2): a warp is 32 adjacent columns of one row (256-byte
+// coalesced segments, conflict-free shared memory, warp-uniform twiddles).
+//   LAST = false: in-place positions, output k of the tile is multiplied by w_n^(prev*low*k) (table lookup).
+//   LAST = true : natural-order (or index-reversed, for the inverse) output rows, optional scale, canonical words.
+template <int B2, bool LAST>
+__global__ void __launch_bounds__(32 << B2) k_pass(const PassParams p)
 {
     constexpr int R2 = 1 << B2;
     constexpr int R = 16 * R2;
-    extern __shared__ u64 smem[];
-    u64 *tile = smem;                               // [R][32]   (only when B2 > 0)
-    u64 *tw = smem + (B2 > 0 ? R * kTileCols : 0);  // [R] output multipliers
-    u64 *pw = tw + R;                               // [32] two-level powers
+    extern __shared__ u64 tile[]; // [R][32]   (only when B2 > 0)
 
     const u32 c = threadIdx.x, t = threadIdx.y;
     const u32 col = blockIdx.y * kTileCols + c;
     const bool colok = col < p.ncols;
     const u64 tau = blockIdx.x;
     const u64 hi = tau >> p.log_rest, low = tau & ((1ULL << p.log_rest) - 1);
-    const u64 rest = 1ULL << p.log_rest;
     const u64 base_in = ((hi * R) << p.log_rest) + low;
-    const bool last = (p.pass + 1 == p.npass);
 
-    // ---- issue the global loads first; the twiddle table is built while they are in flight
     u64 x[16];
 #pragma unroll
     for (int i1 = 0; i1 < 16; i1++) {
-        u64 row = base_in + (((u64)i1 * R2 + t) << p.log_rest);
+        const u64 row = base_in + (((u64)i1 * R2 + t) << p.log_rest);
         x[i1] = (colok && row < p.nvalid) ? p.src[row * p.spitch + col] : 0;
     }
 
-    // ---- per-tile output multipliers tw[k] = base * g^k
-    u64 out_base = 0;
-    bool use_tw;
-    if (last) {
-        // natural output row = digit-reversed(hi) + prev * k
-        u64 rev = 0, h = hi;
-        u32 shift = p.log_prev;
-        for (int q = (int)p.npass - 2; q >= 0; q--) { // digits of hi, least significant = k_{m-1}
-            shift -= p.bits[q];
-            rev |= (h & ((1ULL << p.bits[q]) - 1)) << shift;
-            h >>= p.bits[q];
-        }
-        out_base = rev;
-        use_tw = (p.scale_mode == 2);
-    } else {
-        use_tw = true;
-    }
-    if (use_tw) {
-        const u32 flat = t * 32 + c;
-        if (flat < 32) {
-            u64 g, b;
-            if (last) { // 7^(rev + prev*k) / n
-                g = pow_tab(c_p7, (u32)(1ULL << p.log_prev));
-                b = gl::mul(pow_tab(c_p7, (u32)out_base), c_inv2[p.logn]);
-            } else {    // w_n^(+-prev*low*k)
-                u32 e = (u32)(((low << p.log_prev) & ((1ULL << p.logn) - 1)) << (32 - p.logn));
-                if (p.inverse) e = 0u - e;
-                g = pow_tab(c_w32, e);
-                b = 1;
-            }
-            if (flat < 16) {
-                pw[flat] = gl::pow(g, flat);
-            } else {
-                u64 g16 = g;
-#pragma unroll
-                for (int i = 0; i < 4; i++) g16 = gl::sqr(g16);
-                pw[flat] = gl::mul(b, gl::pow(g16, flat - 16));
-            }
-        }
-        __syncthreads();
-        for (u32 k = t * 32 + c; k < (u32)R; k += 32 * R2) tw[k] = gl::mul(pw[16 + (k >> 4)], pw[k & 15]);
-        // visibility of tw[] is guaranteed by the __syncthreads() below (B2 > 0) or the explicit one (B2 == 0)
-    }
+    // ---- step 1: radix-16 over i1 (row = (i1*R2 + t) within the tile)
+    dft_regs<4>(x);
 
-    // ---- step 1: radix-16 over i1
-    dft_regs<4, INV>(x);
-
-    u64 y[16];
     if (B2 > 0) {
+        // ---- twiddle w_R^(t*k1), exchange through shared memory, step 2: radix-R2 over t
 #pragma unroll
         for (int i = 0; i < 16; i++) {
             const int k1 = bitrev(i, 4);
             u64 v = x[i];
-            if (k1 != 0) { // w_R^(t*k1) = w_256^(t*k1*256/R)
-                u32 e = (t * k1) << (4 - B2);
-                v = gl::mul(v, c_w256[INV ? 1 : 0][e]);
-            }
+            if (k1 != 0) v = gl::mul(v, c_w256[0][(t * k1) << (4 - B2)]); // w_R^(t*k1) = w_256^(t*k1*256/R)
             tile[(k1 * R2 + t) * kTileCols + c] = v;
         }
         __syncthreads();
 #pragma unroll
-        for (int i = 0; i < 16; i++) y[i] = tile[(16 * t + i) * kTileCols + c];
-        Step2<B2>::template run<INV>(y);
-    } else {
-        if (use_tw) __syncthreads();
-#pragma unroll
-        for (int i = 0; i < 16; i++) y[i] = x[i];
+        for (int i = 0; i < 16; i++) x[i] = tile[(16 * t + i) * kTileCols + c];
+        Step2<B2>::run(x);
     }
 
     // ---- store
-    const u64 cscale = (last && p.scale_mode == 1) ? c_inv2[p.logn] : 0;
+    u64 out_base = 0;
+    if (LAST) { // natural output row = digit-reversed(hi) + prev * k
+        u64 h = hi;
+        u32 shift = p.log_prev;
+#pragma unroll
+        for (int q = 2; q >= 0; q--) { // digits of hi, least significant = k_{m-1}; static indices keep p in the param bank
+            if (q <= (int)p.npass - 2) {
+                shift -= p.bits[q];
+                out_base |= (h & ((1ULL << p.bits[q]) - 1)) << shift;
+                h >>= p.bits[q];
+            }
+        }
+    }
+    const u32 tw_shift = p.log_prev + p.log_roots - p.logn;
+    const u64 nmask = (1ULL << p.logn) - 1;
 #pragma unroll
     for (int i = 0; i < 16; i++) {
         u32 k;
@@ -225,12 +205,32 @@ __global__ void __launch_bounds__(32 << B2) k_pass(PassParams p)
         } else {
             k = bitrev(i, 4);
         }
-        u64 v = y[i];
-        if (use_tw) v = gl::mul(v, tw[k]);
-        else if (cscale) v = gl::mul(v, cscale);
-        u64 row = last ? out_base + ((u64)k << p.log_prev) : base_in + ((u64)k << p.log_rest);
-        if (colok) p.dst[row * p.dpitch + col] = gl::canon(v);
+        u64 v = x[i];
+        if (!LAST) {
+            v = gl::mul(v, p.roots[(low * k) << tw_shift]);
+            if (colok) p.dst[(base_in + ((u64)k << p.log_rest)) * p.dpitch + col] = v;
+        } else {
+            u64 row = out_base + ((u64)k << p.log_prev);
+            if (p.inverse) row = (0 - row) & nmask;
+            if (p.scale_mode == 1) v = gl::mul(v, p.cscale);
+            else if (p.scale_mode == 2) v = gl::mul(v, p.rscale[row]);
+            if (colok) p.dst[row * p.dpitch + col] = gl::canon(v);
+        }
     }
+}
+
+// Table builders: roots[i] = w_(2^log_roots)^i ; rscale[i] = 7^i / 2^logn.
+__global__ void k_build_roots(u64 *roots, u32 log_roots)
+{
+    const u64 n = 1ULL << log_roots;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+        roots[i] = gl::canon(pow_tab(c_w32, (u32)(i << (32 - log_roots))));
+}
+__global__ void k_build_rscale(u64 *rscale, u32 logn)
+{
+    const u64 n = 1ULL << logn;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
+        rscale[i] = gl::canon(gl::mul(pow_tab(c_p7, (u32)i), c_inv2[logn]));
 }
 
 // n <= 8: one thread per column, direct O(n^2) evaluation (reference handles these sizes through
