@@ -54,6 +54,10 @@ int gl_dev_alloc(void **dptr, size_t bytes);
 int gl_dev_free(void *dptr);
 int gl_host_alloc(void **hptr, size_t bytes); /* pinned host memory */
 int gl_host_free(void *hptr);
+/* Page-lock an existing host allocation (e.g. the prover's big calloc/mmap arena, prover.cpp:106-119) so that
+ * the *_host calls can overlap their copies with compute; pageable memory works but serialises. */
+int gl_host_register(void *hptr, size_t bytes);
+int gl_host_unregister(void *hptr);
 int gl_h2d(void *dptr, const void *hptr, size_t bytes);
 int gl_d2h(void *hptr, const void *dptr, size_t bytes);
 int gl_sync(void);

@@ -37,6 +37,8 @@ SIGNATURES = {
     "gl_dev_free": (C.c_int, [C.c_void_p]),
     "gl_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "gl_host_free": (C.c_int, [C.c_void_p]),
+    "gl_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
+    "gl_host_unregister": (C.c_int, [C.c_void_p]),
     "gl_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "gl_d2h": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "gl_sync": (C.c_int, []),

@@ -56,6 +56,7 @@ struct Ctx {
     bool ready = false;
     int device = -1;
     cudaStream_t stream = nullptr;
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr; // copy streams of the pipelined host-pointer calls
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     void *arena = nullptr;
     size_t arena_bytes = 0;
@@ -480,6 +481,79 @@ struct DevBuf {
     uint64_t *w() { return (uint64_t *)p; }
 };
 
+// Host-pointer stage commit / extendPol, pipelined over column blocks: while block k is transformed on the
+// compute stream, block k+1 is uploaded (strided 2-D copy out of the row-major host matrix) and the finished
+// block k-1 of the extended matrix is downloaded; the leaf hashing then overlaps the tail of the downloads.
+// PCIe is full duplex, so the wall time approaches max(download time, upload + hashing) instead of the sum.
+// Host buffers should be pinned (gl_host_alloc / gl_host_register) -- pageable memory still works but the
+// copies then serialise.
+int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t *in, u64 n_ext, u64 n, u64 ncols, uint64_t root[4],
+                          bool do_tree)
+{
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "extendPol: bad sizes %llu -> %llu", n, n_ext);
+    if (n_ext > (1ULL << 32)) return fail(GL_ERR_RANGE, "Domain size too big for the curve");
+    const u32 logn = ilog2(n), loge = ilog2(n_ext);
+    DevBuf l, t, stage;
+    TRY(l.alloc((size_t)n_ext * ncols * 8));
+    if (do_tree) TRY(t.alloc(gl_tree_num_elements(n_ext) * 8));
+    u64 *lde = (u64 *)l.p;
+    if (ncols) {
+        // block width: >= 4 blocks when there are enough columns, <= 128 columns, bounded by free memory
+        u64 cb = ((ncols + 3) / 4 + 31) / 32 * 32;
+        if (cb > 128) cb = 128;
+        size_t free_b = 0, total_b = 0;
+        CU(cudaMemGetInfo(&free_b, &total_b));
+        free_b += g.arena_bytes;
+        const size_t per_col = (size_t)(3 * n + n_ext) * 8; // coef + pass scratch + two staging buffers
+        while (cb > 32 && per_col * cb + ((size_t)1 << 30) > free_b) cb -= 32;
+        if (cb > ncols) cb = ncols;
+        TRY(arena_reserve((size_t)(n + n_ext) * cb * 8));
+        TRY(stage.alloc((size_t)2 * n * cb * 8));
+        u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cb;
+        const u64 nb = (ncols + cb - 1) / cb;
+        std::vector<cudaEvent_t> ev_in(nb), ev_done(nb);
+        for (u64 k = 0; k < nb; k++) {
+            CU(cudaEventCreateWithFlags(&ev_in[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
+        }
+        int rc = GL_OK;
+        for (u64 k = 0; k < nb && rc == GL_OK; k++) {
+            const u64 c0 = k * cb;
+            const u32 w = (u32)((ncols - c0 < cb) ? ncols - c0 : cb);
+            u64 *st = (u64 *)stage.p + (k & 1) * (size_t)n * cb;
+            if (k >= 2) cudaStreamWaitEvent(g.s_h2d, ev_done[k - 2], 0); // staging buffer free again
+            cudaMemcpy2DAsync(st, cb * 8, in + c0, ncols * 8, (size_t)w * 8, n, cudaMemcpyHostToDevice, g.s_h2d);
+            cudaEventRecord(ev_in[k], g.s_h2d);
+            cudaStreamWaitEvent(g.stream, ev_in[k], 0);
+            rc = run_ntt(coef, cb, st, cb, tmp, cb, logn, w, true, 2, n);
+            if (rc == GL_OK) rc = run_ntt(lde + c0, ncols, coef, cb, tmp, cb, loge, w, false, 0, n);
+            cudaEventRecord(ev_done[k], g.stream);
+            if (lde_out) {
+                cudaStreamWaitEvent(g.s_d2h, ev_done[k], 0);
+                cudaMemcpy2DAsync(lde_out + c0, ncols * 8, lde + c0, ncols * 8, (size_t)w * 8, n_ext, cudaMemcpyDeviceToHost, g.s_d2h);
+            }
+        }
+        cudaError_t e = cudaGetLastError();
+        if (rc == GL_OK && e != cudaSuccess) rc = fail(GL_ERR_CUDA, "pipelined commit: %s", cudaGetErrorString(e));
+        if (rc != GL_OK) {
+            cudaDeviceSynchronize();
+            for (u64 k = 0; k < nb; k++) { cudaEventDestroy(ev_in[k]); cudaEventDestroy(ev_done[k]); }
+            return rc;
+        }
+        for (u64 k = 0; k < nb; k++) { cudaEventDestroy(ev_in[k]); cudaEventDestroy(ev_done[k]); } // released when complete
+    }
+    if (do_tree) {
+        TRY(merkletree_dev((u64 *)t.p, lde, ncols, n_ext, false));
+        const u64 tw = gl_tree_num_elements(n_ext);
+        if (tree_out) CU(cudaMemcpyAsync(tree_out, t.p, tw * 8, cudaMemcpyDeviceToHost, g.stream));
+        if (root) CU(cudaMemcpyAsync(root, (u64 *)t.p + tw - 4, 32, cudaMemcpyDeviceToHost, g.stream));
+    }
+    CU(cudaStreamSynchronize(g.stream));
+    CU(cudaStreamSynchronize(g.s_d2h));
+    CU(cudaStreamSynchronize(g.s_h2d));
+    return GL_OK;
+}
+
 } // namespace
 
 // =================================================================================================
@@ -506,6 +580,8 @@ int gl_init(int device)
     CU(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10) return fail(GL_ERR_CUDA, "device %s is sm_%d%d; this library is built for sm_100a only", prop.name, prop.major, prop.minor);
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
     for (auto &e : g.ev) CU(cudaEventCreate(&e));
     TRY(upload_tables());
     g.device = device;
@@ -527,7 +603,9 @@ void gl_shutdown(void)
     g.log_roots = g.log_rscale = 0;
     for (auto &e : g.ev) { cudaEventDestroy(e); e = nullptr; }
     cudaStreamDestroy(g.stream);
-    g.stream = nullptr;
+    cudaStreamDestroy(g.s_h2d);
+    cudaStreamDestroy(g.s_d2h);
+    g.stream = g.s_h2d = g.s_d2h = nullptr;
     g.ready = false;
     g.device = -1;
 }
@@ -701,11 +779,7 @@ int gl_extend_pol_host(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64
 {
     if (n == 0 || ncols == 0) return GL_OK;
     TRY(need_ctx());
-    DevBuf d;
-    TRY(d.alloc((size_t)n_ext * ncols * 8));
-    TRY(gl_h2d(d.p, in, (size_t)n * ncols * 8));
-    TRY(gl_extend_pol_dev(d.w(), d.w(), n_ext, n, ncols));
-    return gl_d2h(out, d.p, (size_t)n_ext * ncols * 8);
+    return commit_host_pipelined(out, nullptr, in, n_ext, n, ncols, nullptr, false);
 }
 
 int gl_merkletree_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows)
@@ -725,13 +799,18 @@ int gl_commit_host(uint64_t *lde_out, uint64_t *tree_out, const uint64_t *in, ui
 {
     TRY(need_ctx());
     if (n == 0 || n_ext == 0) return fail(GL_ERR_ARG, "commit: empty domain");
-    DevBuf l, t;
-    TRY(l.alloc((size_t)n_ext * ncols * 8));
-    TRY(t.alloc(gl_tree_num_elements(n_ext) * 8));
-    if (ncols) TRY(gl_h2d(l.p, in, (size_t)n * ncols * 8));
-    TRY(gl_commit_dev(l.w(), t.w(), l.w(), n_ext, n, ncols, root));
-    if (lde_out && ncols) TRY(gl_d2h(lde_out, l.p, (size_t)n_ext * ncols * 8));
-    if (tree_out) TRY(gl_d2h(tree_out, t.p, gl_tree_num_elements(n_ext) * 8));
+    return commit_host_pipelined(lde_out, tree_out, in, n_ext, n, ncols, root, true);
+}
+
+int gl_host_register(void *hptr, size_t bytes)
+{
+    TRY(need_ctx());
+    CU(cudaHostRegister(hptr, bytes, cudaHostRegisterDefault));
+    return GL_OK;
+}
+int gl_host_unregister(void *hptr)
+{
+    CU(cudaHostUnregister(hptr));
     return GL_OK;
 }
 

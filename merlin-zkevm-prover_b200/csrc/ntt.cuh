@@ -141,7 +141,7 @@ template <int B2> struct Step2 {
 //   LAST = false: in-place positions, output k of the tile is multiplied by w_n^(prev*low*k) (table lookup).
 //   LAST = true : natural-order (or index-reversed, for the inverse) output rows, optional scale, canonical words.
 template <int B2, bool LAST>
-__global__ void __launch_bounds__(32 << B2) k_pass(const PassParams p)
+__global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k_pass(const PassParams p)
 {
     constexpr int R2 = 1 << B2;
     constexpr int R = 16 * R2;

@@ -54,6 +54,7 @@ __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
 
 // new[i] = sum_j M[j][i] old[j]  (poseidon_goldilocks.hpp:148-162).  Entries < 64, so the sums of
 // the low and of the high 32-bit halves each fit 64 bits (< 2^42); one 96-bit reduction per output.
+template <int NOUT = 12>
 __device__ __forceinline__ void mds_layer(u64 (&s)[12])
 {
     u32 lo[12], hi[12];
@@ -63,7 +64,7 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
         hi[j] = (u32)(s[j] >> 32);
     }
 #pragma unroll
-    for (int i = 0; i < 12; i++) {
+    for (int i = 0; i < NOUT; i++) {
         u64 L = 0, H = 0;
 #pragma unroll
         for (int j = 0; j < 12; j++) {
@@ -106,10 +107,8 @@ __device__ __forceinline__ void partial_rounds(u64 (&s)[12])
         const u64 t = sbox_add(s[0], c_RCP[r]);
         gl::Dot d;
         d.zero();
-        {
-            const uint4 l = c_SL[r * 12];
-            d.mad(t, l.x, l.y, l.z);
-        }
+        gl::madw(d.c00, (u32)t, 25u); // S[23r] == 25 in every round (checked when the tables are built)
+        gl::madw(d.c10, (u32)(t >> 32), 25u);
 #pragma unroll
         for (int i = 1; i < 12; i++) {
             const uint4 l = c_SL[r * 12 + i];
@@ -121,7 +120,10 @@ __device__ __forceinline__ void partial_rounds(u64 (&s)[12])
     }
 }
 
-// Full permutation, all 12 output words.  Input: any representatives; output: lazily reduced.
+// Full permutation.  Input: any representatives; output: lazily reduced.  OUT4: only s[0..4) of the result
+// are computed (all the sponge and the tree ever read: poseidon_goldilocks.cpp:242-249, 292-295) -- the last
+// MDS layer then costs a third; s[4..12) are left undefined.
+template <bool OUT4 = false>
 __device__ __forceinline__ void permute(u64 (&s)[12])
 {
 #pragma unroll
@@ -133,6 +135,8 @@ __device__ __forceinline__ void permute(u64 (&s)[12])
         if (r == 3) {
             dense_layer(s);
             partial_rounds(s);
+        } else if (OUT4 && r == 7) {
+            mds_layer<4>(s);
         } else {
             mds_layer(s);
         }

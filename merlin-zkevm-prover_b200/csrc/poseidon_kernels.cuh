@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__
     for (u32 c = 0; c < full; c++) {
 #pragma unroll
         for (u32 i = 0; i < 8; i++) s[i] = row_word<PANELS>(rp, p, row, c * 8 + i);
-        permute(s);
+        permute<true>(s);
 #pragma unroll
         for (int i = 0; i < 4; i++) s[8 + i] = s[i];
     }
@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__
     if (rem) {
 #pragma unroll
         for (u32 i = 0; i < 8; i++) s[i] = i < rem ? row_word<PANELS>(rp, p, row, full * 8 + i) : 0;
-        permute(s);
+        permute<true>(s);
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) d[i] = gl::canon(s[i]);
@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(kThreads) k_tree_level(u64 *__restrict__ paren
     }
 #pragma unroll
     for (int i = 8; i < 12; i++) s[i] = 0;
-    permute(s);
+    permute<true>(s);
     ulonglong2 *o = reinterpret_cast<ulonglong2 *>(parents + idx * 4);
     o[0] = make_ulonglong2(gl::canon(s[0]), gl::canon(s[1]));
     o[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
@@ -110,6 +110,7 @@ inline cudaError_t upload_constants()
             rcf[r * 12 + i] = r < 4 ? GLP_RC[(r + 1) * 12 + i] : (r < 7 ? GLP_RC[82 + 12 * (r - 4) + i] : 0);
     for (int r = 0; r < 22; r++) {
         rcp[r] = GLP_RC[60 + r];
+        if (GLP_SP[23 * r] != 25) return cudaErrorInvalidValue; // partial_rounds() hard-codes this coefficient
         for (int i = 0; i < 12; i++) sl[r * 12 + i] = limbs(GLP_SP[23 * r + i]);
         for (int i = 0; i < 11; i++) sv[r * 11 + i] = GLP_SP[23 * r + 12 + i];
     }
