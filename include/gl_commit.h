@@ -75,6 +75,11 @@ int gl_extend_pol_dev(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_
 /* PoseidonGoldilocks::merkletree_avx / MerkleTreeGL::merkelize (poseidon_goldilocks.cpp:266-301,
  * merkleTreeGL.cpp:37-44): tree holds (2*nrows-1)*4 words, leaf digests first, root last. */
 int gl_merkletree_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows);
+/* PoseidonGoldilocks::merkletree_batch_{seq,avx,avx512} (poseidon_goldilocks.cpp:113-164, 302-352, 521-577):
+ * every row is hashed in slices of batch_size columns, the slice digests are hashed again (a different root
+ * from gl_merkletree_*; not called by Starks/MerkleTreeGL, kept for the reference's KATs tests.cpp:2021-2223). */
+int gl_merkletree_batch_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows, uint64_t batch_size);
+int gl_merkletree_batch_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows, uint64_t batch_size);
 /* Starks::genProof stage commit (starks.cpp:52-56): extendPol followed by merkelize.
  * lde (n_ext*ncols words) and tree ((2*n_ext-1)*4 words) are device buffers; root is a HOST
  * pointer to 4 words. */

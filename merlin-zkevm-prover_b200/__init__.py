@@ -46,6 +46,8 @@ SIGNATURES = {
     "gl_ntt_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, C.c_int, C.c_int]),
     "gl_extend_pol_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, _u64]),
     "gl_merkletree_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64]),
+    "gl_merkletree_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, _u64]),
+    "gl_merkletree_batch_host": (C.c_int, [_u64p, _u64p, _u64, _u64, _u64]),
     "gl_commit_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64p]),
     "gl_group_proof_dev": (C.c_int, [_u64p, C.c_void_p, C.c_void_p, _u64, _u64, _u64]),
     "gl_hash_full_result_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64]),
@@ -237,6 +239,15 @@ def merkletree_host(src, nrows=None, ncols=None):
     tree = np.zeros(tree_num_elements(nrows), dtype=np.uint64)
     buf = src if src.size else np.zeros(1, dtype=np.uint64)
     _check(lib().gl_merkletree_host(_p(tree), _p(buf), ncols, nrows))
+    return tree
+
+
+def merkletree_batch_host(src, batch):
+    src = np.ascontiguousarray(src, dtype=np.uint64)
+    nrows, ncols = src.shape
+    tree = np.zeros(tree_num_elements(nrows), dtype=np.uint64)
+    buf = src if src.size else np.zeros(1, dtype=np.uint64)
+    _check(lib().gl_merkletree_batch_host(_p(tree), _p(buf), ncols, nrows, batch))
     return tree
 
 

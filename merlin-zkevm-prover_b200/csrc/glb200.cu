@@ -814,6 +814,37 @@ int gl_host_unregister(void *hptr)
     return GL_OK;
 }
 
+int gl_merkletree_batch_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows, uint64_t batch)
+{
+    TRY(need_ctx());
+    if (nrows == 0) return GL_OK;
+    if (batch == 0) return fail(GL_ERR_ARG, "merkletree_batch: batch size 0");
+    const u64 nb = ncols > 0 ? (ncols + batch - 1) / batch : 1; // poseidon_goldilocks.cpp:122-127
+    DevBuf tmp;
+    TRY(tmp.alloc(nrows * nb * 32));
+    poseidon::k_linear_hash_batches<<<poseidon::grid_for(nrows * nb), poseidon::kThreads, 0, g.stream>>>((u64 *)tmp.p, (const u64 *)src, nrows,
+                                                                                                         (u32)ncols, (u32)batch, (u32)nb);
+    poseidon::launch_linear_hash_rows((u64 *)tree, (const u64 *)tmp.p, nrows, nb * 4, g.stream);
+    g.launches += 2;
+    CU(cudaGetLastError());
+    g.launches += poseidon::launch_tree_levels((u64 *)tree, nrows, g.stream);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_merkletree_batch_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows, uint64_t batch)
+{
+    if (nrows == 0) return GL_OK;
+    TRY(need_ctx());
+    DevBuf s, t;
+    TRY(s.alloc((size_t)nrows * ncols * 8));
+    TRY(t.alloc(gl_tree_num_elements(nrows) * 8));
+    if (ncols) TRY(gl_h2d(s.p, src, (size_t)nrows * ncols * 8));
+    TRY(gl_merkletree_batch_dev(t.w(), s.w(), ncols, nrows, batch));
+    return gl_d2h(tree, t.p, gl_tree_num_elements(nrows) * 8);
+}
+
 int gl_hash_full_result_host(uint64_t *out, const uint64_t *in, uint64_t n)
 {
     if (n == 0) return GL_OK;

@@ -43,15 +43,11 @@ __device__ __forceinline__ u64 row_word(const RowPanels &rp, const u64 *p0, u64 
     return rp.base[g][row * w + (col - rp.start[g])];
 }
 
-// One thread per row (PoseidonGoldilocks::linear_hash, poseidon_goldilocks.cpp:229-265).
+// PoseidonGoldilocks::linear_hash of one row (poseidon_goldilocks.cpp:229-265): sponge, rate 8, capacity 4.
 // ncols <= 4: the row is returned zero-padded WITHOUT hashing (reference :234-239).
 template <bool PANELS>
-__global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__ digests, const RowPanels rp, u64 nrows, u32 ncols)
+__device__ __forceinline__ void linear_hash_row(u64 *d, const RowPanels &rp, const u64 *p, u64 row, u32 ncols)
 {
-    u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= nrows) return;
-    const u64 *p = PANELS ? nullptr : rp.base[0] + row * ncols;
-    u64 *d = digests + row * 4;
     if (ncols <= 4) {
 #pragma unroll
         for (u32 i = 0; i < 4; i++) d[i] = i < ncols ? gl::canon(row_word<PANELS>(rp, p, row, i)) : 0;
@@ -76,6 +72,29 @@ __global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) d[i] = gl::canon(s[i]);
+}
+
+// One thread per row: leaf digests of MerkleTreeGL::merkelize (poseidon_goldilocks.cpp:277-281).
+template <bool PANELS>
+__global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__ digests, const RowPanels rp, u64 nrows, u32 ncols)
+{
+    u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    linear_hash_row<PANELS>(digests + row * 4, rp, PANELS ? nullptr : rp.base[0] + row * ncols, row, ncols);
+}
+
+// merkletree_batch (poseidon_goldilocks.cpp:113-164, 302-352): digest of every `batch`-column slice of every
+// row; thread v = (row, slice).  The per-row digest of these digests is a k_linear_hash_rows over the result.
+__global__ void __launch_bounds__(kThreads) k_linear_hash_batches(u64 *__restrict__ out, const u64 *__restrict__ src, u64 nrows, u32 ncols,
+                                                                  u32 batch, u32 nb)
+{
+    u64 v = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nrows * nb) return;
+    const u64 row = v / nb;
+    const u32 j = (u32)(v - row * nb);
+    const u32 len = j == nb - 1 ? ncols - j * batch : batch;
+    RowPanels rp = {};
+    linear_hash_row<false>(out + v * 4, rp, src + row * ncols + (u64)j * batch, 0, len);
 }
 
 __global__ void __launch_bounds__(kThreads) k_tree_level(u64 *__restrict__ parents, const u64 *__restrict__ children, u64 nparents)

@@ -320,3 +320,76 @@ void glo_fill_xorshift(uint64_t *dst, uint64_t count, uint64_t *state)
     }
     *state = s;
 }
+
+/* ------------------------------------------------- next rows: Q commit, FRI layer commit */
+
+/* Goldilocks3::mul, goldilocks_cubic_extension.hpp:1817-1830 (F_p[x]/(x^3 - x - 1)) */
+void glo_gl3_mul(uint64_t r[3], const uint64_t a[3], const uint64_t b[3])
+{
+    uint64_t A = glo_mul(glo_add(a[0], a[1]), glo_add(b[0], b[1]));
+    uint64_t B = glo_mul(glo_add(a[0], a[2]), glo_add(b[0], b[2]));
+    uint64_t C = glo_mul(glo_add(a[1], a[2]), glo_add(b[1], b[2]));
+    uint64_t D = glo_mul(a[0], b[0]), E = glo_mul(a[1], b[1]), F = glo_mul(a[2], b[2]);
+    uint64_t G = glo_sub(D, E);
+    uint64_t r0 = glo_sub(glo_add(C, G), F);
+    uint64_t r1 = glo_sub(glo_sub(glo_sub(glo_add(A, C), E), E), D);
+    uint64_t r2 = glo_sub(B, G);
+    r[0] = r0; r[1] = r1; r[2] = r2;
+}
+
+/* Starks::genProof step 4, starks.cpp:261-284: q_2ns (n_ext x qdim, evaluations on the coset) ->
+ * cm4_2ns (n_ext x qdim*qdeg): INTT; qq2[k][p] = qq1[p*n + k] * (7^-n)^p for k < n (rows >= n zero);
+ * forward NTT over n_ext. */
+void glo_q_extend(uint64_t *cm4, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim, uint64_t qdeg)
+{
+    uint64_t *qq1 = (uint64_t *)malloc(n_ext * qdim * 8);
+    glo_ntt(qq1, q_2ns, n_ext, qdim, 1, 0);                                  /* :261 */
+    uint64_t w = qdim * qdeg;
+    memset(cm4, 0, n_ext * w * 8);
+    uint64_t shift_in = glo_pow(glo_inv(7), n), cur = 1;                      /* :265 */
+    for (uint64_t p = 0; p < qdeg; p++) {                                    /* :268-280 */
+        for (uint64_t k = 0; k < n; k++)
+            for (uint64_t d = 0; d < qdim; d++)
+                cm4[k * w + p * qdim + d] = (p * n + k < n_ext) ? glo_mul(qq1[(p * n + k) * qdim + d], cur) : 0;
+        cur = glo_mul(cur, shift_in);
+    }
+    glo_ntt(cm4, cm4, n_ext, w, 0, 0);                                       /* :284 */
+    free(qq1);
+}
+
+/* FRIProve::prove folding of one step (si > 0), friProve.cpp:36-107: pol (2^pol_bits x 3) -> out
+ * (2^next_bits x 3).  For group g: INTT of the nX = 2^(pol_bits-next_bits) elements pol[i*pol2N + g],
+ * coefficient i times (shift_inv * w(pol_bits)^-g)^i (polMulAxi :192-200), Horner evaluation at the
+ * cubic-extension challenge x (evalPol :201-217). */
+void glo_fri_fold(uint64_t *out, const uint64_t *pol, unsigned pol_bits, unsigned next_bits, uint64_t shift_inv, const uint64_t x[3])
+{
+    uint64_t pol2n = (uint64_t)1 << next_bits, nx = ((uint64_t)1 << pol_bits) / pol2n;
+    uint64_t wi = glo_inv(glo_root_of_unity(pol_bits));
+#pragma omp parallel for schedule(static)
+    for (uint64_t g = 0; g < pol2n; g++) {
+        uint64_t *ppar = (uint64_t *)malloc(nx * 3 * 8);
+        for (uint64_t i = 0; i < nx; i++) memcpy(ppar + 3 * i, pol + 3 * (i * pol2n + g), 24);
+        glo_ntt(ppar, ppar, nx, 3, 1, 0);
+        uint64_t sinv = glo_mul(shift_inv, glo_pow(wi, g)), r = 1;
+        for (uint64_t i = 0; i < nx; i++) {
+            for (int d = 0; d < 3; d++) ppar[3 * i + d] = glo_mul(ppar[3 * i + d], r);
+            r = glo_mul(r, sinv);
+        }
+        uint64_t acc[3] = {ppar[3 * (nx - 1)], ppar[3 * (nx - 1) + 1], ppar[3 * (nx - 1) + 2]};
+        for (int64_t i = (int64_t)nx - 2; i >= 0; i--) {
+            uint64_t t[3];
+            glo_gl3_mul(t, acc, x);
+            for (int d = 0; d < 3; d++) acc[d] = glo_add(t[d], ppar[3 * i + d]);
+        }
+        for (int d = 0; d < 3; d++) out[3 * g + d] = glo_canon(acc[d]);
+        free(ppar);
+    }
+}
+
+/* FRIProve::getTransposed, friProve.cpp:252-270: aux[i*h + j] = pol[j*w + i], w = 2^transpose_bits, 3-word elements */
+void glo_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, unsigned transpose_bits)
+{
+    uint64_t w = (uint64_t)1 << transpose_bits, h = degree / w;
+    for (uint64_t i = 0; i < w; i++)
+        for (uint64_t j = 0; j < h; j++) memcpy(aux + 3 * (i * h + j), pol + 3 * (j * w + i), 24);
+}

@@ -51,6 +51,15 @@ uint64_t glo_tree_num_elements(uint64_t height);
 uint64_t glo_merkle_proof_size(uint64_t height);
 void glo_group_proof(uint64_t *proof, const uint64_t *source, const uint64_t *nodes,
                      uint64_t height, uint64_t width, uint64_t idx);
+/* Goldilocks3::mul, goldilocks_cubic_extension.hpp:1817-1830 */
+void glo_gl3_mul(uint64_t r[3], const uint64_t a[3], const uint64_t b[3]);
+/* Q-polynomial extension of Starks::genProof step 4, starks.cpp:261-284 (INTT, coset un-shift + (p,k)->(k,p)
+ * transpose, NTT): q_2ns n_ext x qdim -> cm4 n_ext x qdim*qdeg */
+void glo_q_extend(uint64_t *cm4, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim, uint64_t qdeg);
+/* one FRI folding step (si > 0) of FRIProve::prove, friProve.cpp:36-107 */
+void glo_fri_fold(uint64_t *out, const uint64_t *pol, unsigned pol_bits, unsigned next_bits, uint64_t shift_inv, const uint64_t x[3]);
+/* FRIProve::getTransposed, friProve.cpp:252-270 */
+void glo_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, unsigned transpose_bits);
 /* xorshift64 synthetic input of SURVEY 8(c)/(d): seed 88172645463325252, value = s mod p */
 void glo_fill_xorshift(uint64_t *dst, uint64_t count, uint64_t *state);
 int glo_num_threads(void);

@@ -59,6 +59,10 @@ class _Oracle:
             ("glo_merkle_proof_size", u64, [u64]),
             ("glo_group_proof", None, [_u64p, _u64p, _u64p, u64, u64, u64]),
             ("glo_fill_xorshift", None, [_u64p, u64, _u64p]),
+            ("glo_gl3_mul", None, [_u64p, _u64p, _u64p]),
+            ("glo_q_extend", None, [_u64p, _u64p, u64, u64, u64, u64]),
+            ("glo_fri_fold", None, [_u64p, _u64p, C.c_uint, C.c_uint, u64, _u64p]),
+            ("glo_fri_transpose", None, [_u64p, _u64p, u64, C.c_uint]),
             ("glo_num_threads", C.c_int, []),
         ]:
             f = getattr(L, name)
@@ -112,6 +116,27 @@ class _Oracle:
 
     def proof_size(self, height, width):
         return width + 4 * self.L.glo_merkle_proof_size(height)
+
+    def q_extend(self, q_2ns, n, qdeg):
+        q_2ns = np.ascontiguousarray(q_2ns, dtype=np.uint64)
+        n_ext, qdim = q_2ns.shape
+        out = np.zeros((n_ext, qdim * qdeg), dtype=np.uint64)
+        self.L.glo_q_extend(_p(out), _p(q_2ns), n, n_ext, qdim, qdeg)
+        return out
+
+    def fri_fold(self, pol, next_bits, shift_inv, x):
+        pol = np.ascontiguousarray(pol, dtype=np.uint64).reshape(-1, 3)
+        pol_bits = int(pol.shape[0]).bit_length() - 1
+        out = np.zeros((1 << next_bits, 3), dtype=np.uint64)
+        x = np.ascontiguousarray(x, dtype=np.uint64)
+        self.L.glo_fri_fold(_p(out), _p(pol), pol_bits, next_bits, int(shift_inv), _p(x))
+        return out
+
+    def fri_transpose(self, pol, transpose_bits):
+        pol = np.ascontiguousarray(pol, dtype=np.uint64).reshape(-1, 3)
+        aux = np.zeros_like(pol)
+        self.L.glo_fri_transpose(_p(aux), _p(pol), pol.shape[0], transpose_bits)
+        return aux
 
     def group_proof(self, src, nodes, idx):
         src = np.ascontiguousarray(src, dtype=np.uint64)

@@ -72,6 +72,17 @@ def test_merkletree_kats(glb, kats):
     assert np.array_equal(t[-4:], kats["merkle_root_ncols0_131072"])
 
 
+@pytest.mark.gpu
+def test_merkletree_batch(glb, oracle, kats):
+    """PoseidonGoldilocks::merkletree_batch_* (reference KAT tests.cpp:2049-2052) and every node vs the oracle."""
+    t = glb.merkletree_batch_host(fib_rows(64, 128), 32)
+    assert np.array_equal(t[-4:], kats["merkle_batch_root_64x128_b32"]), hexs(t[-4:])
+    rng = np.random.default_rng(11)
+    for (h, w, b) in [(16, 37, 8), (8, 9, 4), (32, 64, 64), (4, 3, 2), (2, 100, 7), (1, 5, 3), (64, 0, 4)]:
+        x = rng.integers(0, P, size=(h, w), dtype=np.uint64)
+        assert np.array_equal(glb.merkletree_batch_host(x, b), oracle.merkletree_batch(x, b)), (h, w, b)
+
+
 def test_merkletree_every_node(glb, oracle, fixtures):
     fin, fout, meta = fixtures["in"], fixtures["out"], fixtures["meta"]
     for (h, w) in meta["tree"]:
