@@ -38,6 +38,7 @@ WORKLOADS = {
     "c2": (23, 24, 600),    # BASELINE configs[1]: batch-proof stage-1 commit shape (the metric's config)
     "c2_665": (23, 24, 665),  # same with the real fork_5 column count
     "c4": (20, 24, 300),    # BASELINE configs[3]: recursive shape, blowup 2^4
+    "c5": (23, 24, 750),    # BASELINE configs[4]: full commit sequence (bench_c5.py); 600+48+96 stage columns + 6 Q columns
     "small": (18, 19, 64),
     "mid": (20, 21, 256),    # profiling shape: row pitch 2 KiB, fits ncu kernel replay
 }
@@ -208,6 +209,10 @@ def main():
     if world > 1:
         import bench_mgpu
         return bench_mgpu.run(args, glb, dist, rank, world, local_rank, config, WORKLOADS)
+
+    if args.workload == "c5":
+        import bench_c5
+        return bench_c5.run(args, glb, config, peaks, ClockSampler, SEED)
 
     din = glb.DeviceBuffer(n * ncols)
     dlde = glb.DeviceBuffer(e * ncols)

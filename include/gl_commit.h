@@ -122,6 +122,26 @@ uint64_t gl_merkle_proof_size(uint64_t height);
  *      (CUDA events on the library stream), in milliseconds: [0] LDE, [1] leaf hashing, [2] tree levels */
 int gl_last_timings(float ms[3]);
 
+/* ---- callers either side of the stage commit, device-resident -------------------------------- */
+/* Starks::genProof step 4 (starks.cpp:261-284): q_2ns (n_ext x qdim evaluations on the coset) -> cm4_2ns
+ * (n_ext x qdim*qdeg): INTT, coset un-shift by (7^-n)^p with the (p,k)->(k,p) regrouping, NTT.  qdeg*n <= n_ext. */
+int gl_q_extend_dev(uint64_t *cm4, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim, uint64_t qdeg);
+/* ... followed by treesGL[3]->merkelize() / getRoot (starks.cpp:289-290).  root: HOST pointer. */
+int gl_q_commit_dev(uint64_t *cm4, uint64_t *tree, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim,
+                    uint64_t qdeg, uint64_t root[4]);
+/* One folding step of FRIProve::prove (friProve.cpp:36-107, si > 0): pol (2^pol_bits x 3) -> out (2^next_bits x 3)
+ * evaluated at the F_p^3 challenge x (HOST pointer, 3 words); shift_inv is polShiftInv of that step.
+ * Asynchronous on the library stream (gl_sync or a later synchronous call orders it). */
+int gl_fri_fold_dev(uint64_t *out, const uint64_t *pol, uint32_t pol_bits, uint32_t next_bits, uint64_t shift_inv,
+                    const uint64_t x[3]);
+/* FRIProve::getTransposed (friProve.cpp:252-270) on 3-word elements; asynchronous. */
+int gl_fri_transpose_dev(uint64_t *aux, const uint64_t *pol, uint64_t degree, uint32_t transpose_bits);
+/* fold + getTransposed + MerkleTreeGL(2^tree_bits, 3 * 2^(next_bits-tree_bits)).merkelize() + getRoot
+ * (friProve.cpp:36-126).  pol2 (2^next_bits x 3) and aux (same size, the tree's source) are outputs. */
+int gl_fri_layer_commit_dev(uint64_t *tree, uint64_t *aux, uint64_t *pol2, const uint64_t *pol, uint32_t pol_bits,
+                            uint32_t next_bits, uint32_t tree_bits, uint64_t shift_inv, const uint64_t x[3],
+                            uint64_t root[4]);
+
 /* [0] LDE, [1] leaf hashing, [2] tree levels (incl. the gathered top), [3] multi-GPU exchange */
 int gl_last_timings4(float ms[4]);
 

@@ -63,6 +63,11 @@ SIGNATURES = {
     "gl_tree_num_elements": (_u64, [_u64]),
     "gl_merkle_proof_size": (_u64, [_u64]),
     "gl_last_timings": (C.c_int, [C.POINTER(C.c_float)]),
+    "gl_q_extend_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64]),
+    "gl_q_commit_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64, _u64p]),
+    "gl_fri_fold_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, _u64, _u64p]),
+    "gl_fri_transpose_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, C.c_uint32]),
+    "gl_fri_layer_commit_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, _u64, _u64p, _u64p]),
     "gl_last_timings4": (C.c_int, [C.POINTER(C.c_float)]),
     "gl_mgpu_unique_id": (C.c_int, [C.POINTER(C.c_uint8)]),
     "gl_mgpu_init": (C.c_int, [C.POINTER(C.c_uint8), C.c_int, C.c_int]),
@@ -333,3 +338,18 @@ def mgpu_gather_tree(tree_full, subtree, n_ext):
 
 def fill_synthetic_cols_dev(ptr, nrows, col0, ncols_local, ncols_total, seed=1):
     _check(lib().gl_fill_synthetic_cols_dev(C.c_void_p(ptr), nrows, col0, ncols_local, ncols_total, seed))
+
+
+# ---- next rows: Q-polynomial commit, FRI layer commit (device-resident) -----------------------------
+def q_commit_dev(cm4, tree, q_2ns, n, n_ext, qdim, qdeg):
+    root = np.zeros(4, dtype=np.uint64)
+    _check(lib().gl_q_commit_dev(C.c_void_p(cm4), C.c_void_p(tree), C.c_void_p(q_2ns), n, n_ext, qdim, qdeg, _p(root)))
+    return root
+
+
+def fri_layer_commit_dev(tree, aux, pol2, pol, pol_bits, next_bits, tree_bits, shift_inv, x):
+    root = np.zeros(4, dtype=np.uint64)
+    x = np.ascontiguousarray(x, dtype=np.uint64)
+    _check(lib().gl_fri_layer_commit_dev(C.c_void_p(tree), C.c_void_p(aux), C.c_void_p(pol2), C.c_void_p(pol), pol_bits, next_bits,
+                                         tree_bits, int(shift_inv), _p(x), _p(root)))
+    return root

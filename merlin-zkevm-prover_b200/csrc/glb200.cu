@@ -6,6 +6,7 @@
 #include "../../include/gl_commit.h"
 #include "ntt.cuh"
 #include "poseidon_kernels.cuh"
+#include "fri.cuh"
 
 #include <dlfcn.h>
 #include <nccl.h> // types and prototypes only: libnccl.so.2 is dlopen'ed by gl_mgpu_init (single-GPU users need no NCCL)
@@ -1019,6 +1020,88 @@ int gl_fill_synthetic_cols_dev(uint64_t *dst, uint64_t nrows, uint64_t col0, uin
     CU(cudaGetLastError());
     CU(cudaStreamSynchronize(g.stream));
     return GL_OK;
+}
+
+// ---- next rows: Q-polynomial commit, FRI layer commit -----------------------------------
+int gl_q_extend_dev(uint64_t *cm4, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim, uint64_t qdeg)
+{
+    TRY(need_ctx());
+    if (n == 0 || qdim == 0 || qdeg == 0) return GL_OK;
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "q_extend: bad sizes %llu -> %llu", (u64)n, (u64)n_ext);
+    if (qdeg > (u64)fri::kMaxQDeg || qdeg * n > n_ext) return fail(GL_ERR_ARG, "q_extend: qDeg %llu out of range", (u64)qdeg);
+    const u64 w = qdim * qdeg;
+    const u32 loge = ilog2(n_ext);
+    DevBuf qq1, qq2;
+    TRY(qq1.alloc(n_ext * qdim * 8));
+    TRY(qq2.alloc(n * w * 8));
+    CU(cudaEventRecord(g.ev[0], g.stream));
+    TRY(ntt_dev((u64 *)qq1.p, (const u64 *)q_2ns, n_ext, qdim, 1, 0));                    // starks.cpp:261
+    fri::QScale sc;
+    const u64 shift_in = hpow(hpow(7, P - 2), n);                                        // (1/7)^N, starks.cpp:265
+    sc.s[0] = 1;
+    for (int p = 1; p < fri::kMaxQDeg; p++) sc.s[p] = hmul(sc.s[p - 1], shift_in);
+    fri::k_q_regroup<<<148 * 8, 256, 0, g.stream>>>((u64 *)qq2.p, (const u64 *)qq1.p, n, (u32)qdim, (u32)qdeg, sc); // :268-280
+    g.launches++;
+    CU(cudaGetLastError());
+    // forward NTT over the extended domain; rows >= n of qq2 are zeros (:284)
+    u32 cb = pick_col_block(w, n_ext * 8);
+    if (loge > 8) TRY(arena_reserve((size_t)n_ext * cb * 8));
+    for (u64 c0 = 0; c0 < w; c0 += cb) {
+        u32 ww = (u32)((w - c0 < cb) ? w - c0 : cb);
+        TRY(run_ntt((u64 *)cm4 + c0, w, (const u64 *)qq2.p + c0, w, (u64 *)g.arena, cb, loge, ww, false, 0, n));
+    }
+    CU(cudaEventRecord(g.ev[1], g.stream));
+    return collect_timings(true, false);
+}
+
+int gl_q_commit_dev(uint64_t *cm4, uint64_t *tree, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim, uint64_t qdeg,
+                    uint64_t root[4])
+{
+    TRY(gl_q_extend_dev(cm4, q_2ns, n, n_ext, qdim, qdeg));
+    const float lde_ms = g.ms[0];
+    TRY(merkletree_dev((u64 *)tree, (const u64 *)cm4, qdim * qdeg, n_ext, true));          // starks.cpp:289
+    if (root) CU(cudaMemcpyAsync(root, tree + gl_tree_num_elements(n_ext) - 4, 32, cudaMemcpyDeviceToHost, g.stream));
+    TRY(collect_timings(false, true));
+    g.ms[0] = lde_ms;
+    return GL_OK;
+}
+
+int gl_fri_fold_dev(uint64_t *out, const uint64_t *pol, uint32_t pol_bits, uint32_t next_bits, uint64_t shift_inv, const uint64_t x[3])
+{
+    TRY(need_ctx());
+    if (next_bits > pol_bits || pol_bits > 32 || pol_bits - next_bits > 6) return fail(GL_ERR_ARG, "fri_fold: bits %u -> %u unsupported", pol_bits, next_bits);
+    TRY(ensure_roots(pol_bits));
+    fri::F3 xx = {x[0], x[1], x[2]};
+    const u64 pol2n = 1ULL << next_bits;
+    const u64 nx_inv = hpow((P + 1) / 2, pol_bits - next_bits);
+    fri::k_fri_fold<<<(unsigned)((pol2n + 127) / 128), 128, 0, g.stream>>>((u64 *)out, (const u64 *)pol, pol_bits, next_bits, shift_inv, xx, g.roots,
+                                                                           g.log_roots, nx_inv);
+    g.launches++;
+    CU(cudaGetLastError());
+    return GL_OK;
+}
+
+int gl_fri_transpose_dev(uint64_t *aux, const uint64_t *pol, uint64_t degree, uint32_t transpose_bits)
+{
+    TRY(need_ctx());
+    if (degree == 0) return GL_OK;
+    if ((degree >> transpose_bits) == 0) return fail(GL_ERR_ARG, "fri_transpose: 2^%u columns exceed the degree", transpose_bits);
+    fri::k_fri_transpose<<<148 * 8, 256, 0, g.stream>>>((u64 *)aux, (const u64 *)pol, degree, transpose_bits);
+    g.launches++;
+    CU(cudaGetLastError());
+    return GL_OK;
+}
+
+int gl_fri_layer_commit_dev(uint64_t *tree, uint64_t *aux, uint64_t *pol2, const uint64_t *pol, uint32_t pol_bits, uint32_t next_bits,
+                            uint32_t tree_bits, uint64_t shift_inv, const uint64_t x[3], uint64_t root[4])
+{
+    if (tree_bits > next_bits) return fail(GL_ERR_ARG, "fri_layer: tree of 2^%u groups from 2^%u elements", tree_bits, next_bits);
+    TRY(gl_fri_fold_dev(pol2, pol, pol_bits, next_bits, shift_inv, x));                    // friProve.cpp:36-107
+    const u64 pol2n = 1ULL << next_bits, ngroups = 1ULL << tree_bits, group = pol2n / ngroups;
+    TRY(gl_fri_transpose_dev(aux, pol2, pol2n, tree_bits));                                // :112-117
+    TRY(merkletree_dev((u64 *)tree, (const u64 *)aux, group * 3, ngroups, true));          // :120-123
+    if (root) CU(cudaMemcpyAsync(root, tree + gl_tree_num_elements(ngroups) - 4, 32, cudaMemcpyDeviceToHost, g.stream));
+    return collect_timings(false, true);
 }
 
 int gl_last_timings4(float ms[4])

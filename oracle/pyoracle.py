@@ -172,6 +172,9 @@ class _Ref:
             ("ref_group_proof", None, [_u64p, _u64p, _u64p, u64, u64, u64]),
             ("ref_commit", None, [_u64p, _u64p, _u64p, u64, u64, u64, _u64p,
                                   C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+            ("ref_gl3_mul", None, [_u64p, _u64p, _u64p]),
+            ("ref_q_extend", None, [_u64p, _u64p, u64, u64, u64, u64]),
+            ("ref_fri_fold", None, [_u64p, _u64p, C.c_uint, C.c_uint, u64, _u64p]),
         ]:
             f = getattr(L, name)
             f.restype = res
@@ -236,6 +239,28 @@ class _Ref:
         proof = np.zeros(self.L.ref_proof_size(h, w), dtype=np.uint64)
         self.L.ref_group_proof(_p(proof), _p(src), _p(nodes), h, w, idx)
         return self.canon(proof)
+
+    def gl3_mul(self, a, b):
+        a = np.ascontiguousarray(a, dtype=np.uint64).copy()
+        b = np.ascontiguousarray(b, dtype=np.uint64).copy()
+        r = np.zeros(3, dtype=np.uint64)
+        self.L.ref_gl3_mul(_p(r), _p(a), _p(b))
+        return self.canon(r)
+
+    def q_extend(self, q_2ns, n, qdeg):
+        q_2ns = np.ascontiguousarray(q_2ns, dtype=np.uint64).copy()
+        n_ext, qdim = q_2ns.shape
+        out = np.zeros((n_ext, qdim * qdeg), dtype=np.uint64)
+        self.L.ref_q_extend(_p(out), _p(q_2ns), n, n_ext, qdim, qdeg)
+        return self.canon(out)
+
+    def fri_fold(self, pol, next_bits, shift_inv, x):
+        pol = np.ascontiguousarray(pol, dtype=np.uint64).reshape(-1, 3).copy()
+        pol_bits = int(pol.shape[0]).bit_length() - 1
+        out = np.zeros((1 << next_bits, 3), dtype=np.uint64)
+        x = np.ascontiguousarray(x, dtype=np.uint64).copy()
+        self.L.ref_fri_fold(_p(out), _p(pol), pol_bits, next_bits, int(shift_inv), _p(x))
+        return self.canon(out)
 
     def commit(self, src, n_ext, want_lde=True):
         """extendPol + merkelize (starks.cpp:52-56); returns (lde, tree, ms_lde, ms_tree)."""

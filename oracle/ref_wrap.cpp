@@ -13,6 +13,8 @@
 #include "ntt_goldilocks.hpp"
 #include "poseidon_goldilocks.hpp"
 #include "merkleTreeGL.hpp"
+#include "goldilocks_cubic_extension.hpp"
+#include <vector>
 #include <omp.h>
 
 typedef Goldilocks::Element E;
@@ -137,6 +139,61 @@ void ref_commit(uint64_t *lde, uint64_t *in, uint64_t *tree, uint64_t n_ext, uin
     double t2 = omp_get_wtime();
     if (ms_lde) *ms_lde = (t1 - t0) * 1e3;
     if (ms_tree) *ms_tree = (t2 - t1) * 1e3;
+}
+
+// ---- next rows.  The callers below live in Starks::genProof / FRIProve::prove, which cannot be
+// compiled stand-alone (StarkInfo, Transcript, zklog ...).  Their loop bodies are restated here line by line
+// on top of the reference's OWN arithmetic (NTT_Goldilocks, Goldilocks::*, Goldilocks3::mul), which is what
+// pins the oracle restatement in gl_oracle.c.
+
+void ref_gl3_mul(uint64_t *r, uint64_t *a, uint64_t *b)
+{
+    Goldilocks3::mul((Goldilocks3::Element &)*(E *)r, (Goldilocks3::Element &)*(E *)a, (Goldilocks3::Element &)*(E *)b);
+}
+
+// src/starkpil/starks.cpp:261-284
+void ref_q_extend(uint64_t *cm4, uint64_t *q_2ns, uint64_t N, uint64_t NExtended, uint64_t qDim, uint64_t qDeg)
+{
+    NTT_Goldilocks nttExtended(NExtended);
+    std::vector<E> qq1(NExtended * qDim), qq2(NExtended * qDeg * qDim, Goldilocks::zero());
+    nttExtended.INTT(qq1.data(), (E *)q_2ns, NExtended, qDim, NULL, 2, 1);
+    E shiftIn = Goldilocks::exp(Goldilocks::inv(Goldilocks::shift()), N);
+    E curS = Goldilocks::one();
+    for (uint64_t p = 0; p < qDeg; p++) {
+        for (uint64_t k = 0; k < N; ++k)
+            for (uint64_t d = 0; d < qDim; d++) qq2[(k * qDeg + p) * qDim + d] = qq1[(p * N + k) * qDim + d] * curS;
+        curS = Goldilocks::mul(curS, shiftIn);
+    }
+    nttExtended.NTT((E *)cm4, qq2.data(), NExtended, qDim * qDeg);
+}
+
+// src/starkpil/fri/friProve.cpp:36-107 (si > 0 branch), polMulAxi :192-200, evalPol :201-217
+void ref_fri_fold(uint64_t *out, uint64_t *pol, unsigned polBits, unsigned nextBits, uint64_t shiftInv, uint64_t *x)
+{
+    uint64_t pol2N = 1ULL << nextBits, nX = (1ULL << polBits) / pol2N;
+    E wi = Goldilocks::inv(Goldilocks::w(polBits));
+    E sinv_ = Goldilocks::fromU64(shiftInv);
+    E *fp = (E *)pol, *o = (E *)out;
+    for (uint64_t g = 0; g < pol2N; g++) {
+        std::vector<E> ppar(nX * 3), ppar_c(nX * 3);
+        for (uint64_t i = 0; i < nX; i++)
+            for (int d = 0; d < 3; d++) ppar[i * 3 + d] = fp[((i * pol2N) + g) * 3 + d];
+        NTT_Goldilocks ntt(nX, 1);
+        ntt.INTT(ppar_c.data(), ppar.data(), nX, 3);
+        E r = Goldilocks::one();
+        for (uint64_t i = 0; i < nX; i++) {
+            for (int d = 0; d < 3; d++) ppar_c[i * 3 + d] = ppar_c[i * 3 + d] * r;
+            r = r * sinv_;
+        }
+        E res[3] = {ppar_c[(nX - 1) * 3], ppar_c[(nX - 1) * 3 + 1], ppar_c[(nX - 1) * 3 + 2]};
+        for (int64_t i = (int64_t)nX - 2; i >= 0; i--) {
+            E aux[3];
+            Goldilocks3::mul((Goldilocks3::Element &)aux[0], (Goldilocks3::Element &)res[0], (Goldilocks3::Element &)*(E *)x);
+            for (int d = 0; d < 3; d++) res[d] = aux[d] + ppar_c[i * 3 + d];
+        }
+        for (int d = 0; d < 3; d++) o[g * 3 + d] = res[d];
+        sinv_ = sinv_ * wi;
+    }
 }
 
 } // extern "C"

@@ -49,6 +49,14 @@ def fixtures():
         inputs["lde_%d_%d_%d" % (n, e, c)] = rng.integers(0, P, size=(n, c), dtype=np.uint64)
     for (h, w) in meta["tree"]:
         inputs["tree_%d_%d" % (h, w)] = rng.integers(0, P, size=(h, w), dtype=np.uint64)
+    rng2 = np.random.default_rng(meta.get("seed2", 0))
+    for (n, e, qdeg) in meta.get("q_extend", []):
+        inputs["qext_%d_%d_%d" % (n, e, qdeg)] = rng2.integers(0, P, size=(e, 3), dtype=np.uint64)
+    for (pb, nb) in meta.get("fri_fold", []):
+        pol = rng2.integers(0, P, size=(1 << pb, 3), dtype=np.uint64)
+        x = rng2.integers(0, P, size=3, dtype=np.uint64)
+        si = int(rng2.integers(1, P, dtype=np.uint64))
+        inputs["frifold_%d_%d" % (pb, nb)] = (pol, x, si)
     return {"out": fx, "in": inputs, "meta": meta}
 
 

@@ -260,3 +260,50 @@ def test_full_size_lde_sampled_columns_and_linearity(glb, oracle):
     s = glb.field_op_host("add", a.reshape(-1), b.reshape(-1)).reshape(n, c)
     gs = glb.extend_pol_host(s, e)
     assert np.array_equal(gs.reshape(-1), glb.field_op_host("add", got.reshape(-1), gb.reshape(-1)))
+
+
+@pytest.mark.gpu
+def test_q_polynomial_commit(glb, oracle, fixtures):
+    """Starks::genProof step 4 (starks.cpp:261-290): INTT, coset un-shift + regroup, NTT, merkelize."""
+    shapes = [(n, e, qdeg, fixtures["in"]["qext_%d_%d_%d" % (n, e, qdeg)]) for (n, e, qdeg) in fixtures["meta"]["q_extend"]]
+    rng = np.random.default_rng(21)
+    shapes.append((1 << 10, 1 << 12, 3, rng.integers(0, P, size=(1 << 12, 3), dtype=np.uint64)))
+    for (n, e, qdeg, q) in shapes:
+        dq = glb.DeviceBuffer(e * 3).upload(q)
+        dcm4 = glb.DeviceBuffer(e * 3 * qdeg)
+        dtree = glb.DeviceBuffer(glb.tree_num_elements(e))
+        root = glb.q_commit_dev(dcm4.ptr, dtree.ptr, dq.ptr, n, e, 3, qdeg)
+        want = oracle.q_extend(q, n, qdeg)
+        key = "qext_%d_%d_%d" % (n, e, qdeg)
+        if key in fixtures["out"]:
+            assert np.array_equal(want, fixtures["out"][key])
+        assert np.array_equal(dcm4.download().reshape(e, 3 * qdeg), want), (n, e, qdeg)
+        wt = oracle.merkletree(want)
+        assert np.array_equal(dtree.download(), wt)
+        assert np.array_equal(root, wt[-4:])
+
+
+@pytest.mark.gpu
+def test_fri_layer_commit(glb, oracle, fixtures):
+    """FRIProve::prove one layer (friProve.cpp:36-126): fold in F_p^3, getTransposed, MerkleTreeGL merkelize."""
+    cases = [(pb, nb, fixtures["in"]["frifold_%d_%d" % (pb, nb)]) for (pb, nb) in fixtures["meta"]["fri_fold"]]
+    rng = np.random.default_rng(22)
+    cases.append((14, 10, (rng.integers(0, P, size=(1 << 14, 3), dtype=np.uint64), rng.integers(0, P, size=3, dtype=np.uint64), 12345678901234567)))
+    cases.append((11, 5, (rng.integers(0, P, size=(1 << 11, 3), dtype=np.uint64), rng.integers(0, P, size=3, dtype=np.uint64), 7)))
+    for (pb, nb, (pol, x, si)) in cases:
+        want = oracle.fri_fold(pol, nb, si, x)
+        key = "frifold_%d_%d" % (pb, nb)
+        if key in fixtures["out"]:
+            assert np.array_equal(want, fixtures["out"][key])
+        for tb in sorted({max(nb - 2, 0), nb}):
+            dpol = glb.DeviceBuffer((1 << pb) * 3).upload(pol)
+            dpol2 = glb.DeviceBuffer((1 << nb) * 3)
+            daux = glb.DeviceBuffer((1 << nb) * 3)
+            dtree = glb.DeviceBuffer(glb.tree_num_elements(1 << tb))
+            root = glb.fri_layer_commit_dev(dtree.ptr, daux.ptr, dpol2.ptr, dpol.ptr, pb, nb, tb, si, x)
+            assert np.array_equal(dpol2.download().reshape(-1, 3), want), (pb, nb)
+            aux = oracle.fri_transpose(want, tb)
+            assert np.array_equal(daux.download().reshape(-1, 3), aux)
+            wt = oracle.merkletree(aux.reshape(1 << tb, -1))
+            assert np.array_equal(dtree.download(), wt), (pb, nb, tb)
+            assert np.array_equal(root, wt[-4:])

@@ -129,3 +129,25 @@ def test_oracle_vs_live_reference(oracle, ref):
     # nphase / nblock only change the reference's blocking, never the result (tests.cpp:2253-2384)
     for nphase, nblock in [(1, 1), (2, 3), (4, 11), (9, 2)]:
         assert np.array_equal(ref.ntt(a, nphase=nphase, nblock=nblock), oracle.ntt(a))
+
+
+def test_next_rows_match_reference_fixtures(oracle, fixtures):
+    """Q-polynomial extension (starks.cpp:261-284) and FRI folding (friProve.cpp:36-107) of the oracle against
+    fixtures produced with the reference's own NTT / Goldilocks3 arithmetic (oracle/ref_wrap.cpp)."""
+    for (n, e, qdeg) in fixtures["meta"]["q_extend"]:
+        k = "qext_%d_%d_%d" % (n, e, qdeg)
+        assert np.array_equal(oracle.q_extend(fixtures["in"][k], n, qdeg), fixtures["out"][k]), k
+    for (pb, nb) in fixtures["meta"]["fri_fold"]:
+        k = "frifold_%d_%d" % (pb, nb)
+        pol, x, si = fixtures["in"][k]
+        assert np.array_equal(oracle.fri_fold(pol, nb, si, x), fixtures["out"][k]), k
+
+
+def test_fri_transpose_is_the_reference_index_map(oracle):
+    # friProve.cpp:252-270: aux[i*h + j] = pol[j*w + i]
+    pol = np.arange(3 * 64, dtype=np.uint64).reshape(64, 3)
+    aux = oracle.fri_transpose(pol, 4)
+    w, h = 16, 4
+    for i in range(w):
+        for j in range(h):
+            assert np.array_equal(aux[i * h + j], pol[j * w + i])
