@@ -142,6 +142,14 @@ int gl_fri_layer_commit_dev(uint64_t *tree, uint64_t *aux, uint64_t *pol2, const
                             uint32_t next_bits, uint32_t tree_bits, uint64_t shift_inv, const uint64_t x[3],
                             uint64_t root[4]);
 
+/* Offline constant tree, the `bctree` tool (tools/starkpil/bctree/build_const_tree.cpp:333-407, GL branch): the
+ * .consttree image [nPols, nExt, nExt x nPols extended constants, (2 nExt - 1) x 4 nodes] that
+ * MerkleTreeGL(Goldilocks::Element *tree) re-opens (merkleTreeGL.hpp:24-32, starks.hpp:190).  Its interpolate()
+ * (:198-330) is the same coset extension as extendPol (coefficients * 7^i / n).  HOST buffers; const_tree holds
+ * gl_consttree_num_elements(npols, n_ext) words; the verification key is its last 4 words (:386-392). */
+uint64_t gl_consttree_num_elements(uint64_t npols, uint64_t n_ext);
+int gl_build_consttree_host(uint64_t *const_tree, const uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols);
+
 /* [0] LDE, [1] leaf hashing, [2] tree levels (incl. the gathered top), [3] multi-GPU exchange */
 int gl_last_timings4(float ms[4]);
 

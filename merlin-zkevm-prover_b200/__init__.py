@@ -68,6 +68,8 @@ SIGNATURES = {
     "gl_fri_fold_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, _u64, _u64p]),
     "gl_fri_transpose_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, C.c_uint32]),
     "gl_fri_layer_commit_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, _u64, _u64p, _u64p]),
+    "gl_consttree_num_elements": (_u64, [_u64, _u64]),
+    "gl_build_consttree_host": (C.c_int, [_u64p, _u64p, _u64, _u64, _u64]),
     "gl_last_timings4": (C.c_int, [C.POINTER(C.c_float)]),
     "gl_mgpu_unique_id": (C.c_int, [C.POINTER(C.c_uint8)]),
     "gl_mgpu_init": (C.c_int, [C.POINTER(C.c_uint8), C.c_int, C.c_int]),
@@ -353,3 +355,12 @@ def fri_layer_commit_dev(tree, aux, pol2, pol, pol_bits, next_bits, tree_bits, s
     _check(lib().gl_fri_layer_commit_dev(C.c_void_p(tree), C.c_void_p(aux), C.c_void_p(pol2), C.c_void_p(pol), pol_bits, next_bits,
                                          tree_bits, int(shift_inv), _p(x), _p(root)))
     return root
+
+
+def build_consttree_host(const_pols, n_ext):
+    """The .consttree image of tools/starkpil/bctree: [nPols, nExt, extended constants, nodes]."""
+    const_pols = np.ascontiguousarray(const_pols, dtype=np.uint64)
+    n, npols = const_pols.shape
+    out = np.zeros(int(lib().gl_consttree_num_elements(npols, n_ext)), dtype=np.uint64)
+    _check(lib().gl_build_consttree_host(_p(out), _p(const_pols), n, n_ext, npols))
+    return out

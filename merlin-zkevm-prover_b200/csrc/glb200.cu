@@ -1104,6 +1104,18 @@ int gl_fri_layer_commit_dev(uint64_t *tree, uint64_t *aux, uint64_t *pol2, const
     return collect_timings(false, true);
 }
 
+// ---- offline constant tree (tools/starkpil/bctree/build_const_tree.cpp:333-407) -------------------------
+uint64_t gl_consttree_num_elements(uint64_t npols, uint64_t n_ext) { return 2 + npols * n_ext + gl_tree_num_elements(n_ext); }
+
+int gl_build_consttree_host(uint64_t *const_tree, const uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols)
+{
+    TRY(need_ctx());
+    if (n == 0 || n_ext == 0 || npols == 0) return fail(GL_ERR_ARG, "buildConstTree: empty input");
+    const_tree[0] = npols; // header read back by MerkleTreeGL(Goldilocks::Element *tree), merkleTreeGL.hpp:24-32
+    const_tree[1] = n_ext;
+    return commit_host_pipelined(const_tree + 2, const_tree + 2 + npols * n_ext, const_pols, n_ext, n, npols, nullptr, true);
+}
+
 int gl_last_timings4(float ms[4])
 {
     for (int i = 0; i < 4; i++) ms[i] = g.ms[i];

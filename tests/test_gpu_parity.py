@@ -307,3 +307,35 @@ def test_fri_layer_commit(glb, oracle, fixtures):
             wt = oracle.merkletree(aux.reshape(1 << tb, -1))
             assert np.array_equal(dtree.download(), wt), (pb, nb, tb)
             assert np.array_equal(root, wt[-4:])
+
+
+@pytest.mark.gpu
+def test_consttree_image(glb, oracle):
+    """bctree (build_const_tree.cpp:333-407): [nPols, nExt, extended constants, nodes] re-opened as MerkleTreeGL."""
+    rng = np.random.default_rng(23)
+    for (n, e, c) in [(64, 128, 5), (256, 1024, 18), (16, 256, 1)]:
+        x = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+        img = glb.build_consttree_host(x, e)
+        lde = oracle.extend_pol(x, e)
+        tree = oracle.merkletree(lde)
+        assert img[0] == c and img[1] == e and img.size == 2 + c * e + tree.size
+        assert np.array_equal(img[2:2 + c * e].reshape(e, c), lde)
+        assert np.array_equal(img[2 + c * e:], tree)
+        # the view MerkleTreeGL(Element *tree) takes (merkleTreeGL.hpp:24-32): width, height, source, nodes
+        w, h = int(img[0]), int(img[1])
+        proof = oracle.group_proof(img[2:2 + h * w].reshape(h, w), img[2 + h * w:], 3)
+        assert np.array_equal(proof[:w], lde[3])
+
+
+@pytest.mark.gpu
+def test_cpp_shims_run_reference_tests(glb):
+    """host/test_shims: the reference's gtest cases (tests.cpp merkletree/ntt/extendePol + the starks.cpp:52-56 sequence)
+    compiled against the drop-in C++ classes (NTT_Goldilocks, MerkleTreeGL, PoseidonGoldilocks) over the C ABI."""
+    import os
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "merlin-zkevm-prover_b200", "host", "test_shims")
+    if not os.path.exists(exe):
+        subprocess.run(["make", "-C", os.path.dirname(exe)], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
