@@ -245,14 +245,26 @@ def main():
     leaf_perm, tree_perm = permutations(loge, ncols)
     leaf_bytes = e * ncols * 8 + e * 32                 # read the extended matrix once, write the digests
     lde_bytes, lde_passes = lde_pass_bytes(logn, loge, ncols)
+    sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+    # ncu (profiles/r1_07_leaf_ncu.txt): 19,057 warp instructions per permutation in k_linear_hash_rows; DRAM traffic
+    # 1.005x the algorithmic bytes (4.384 GB moved for 4.362 GB on the 2^21 x 256 capture; a c2 launch is too long to replay)
+    INSTR_PER_PERM, TRAFFIC_RATIO = 19057.0, 1.005
+    ipc = leaf_perm / (phase["leaf_ms"] / 1e3) / 32 * INSTR_PER_PERM / (148 * 4 * sm_hz)
     roofline = {"kernel": "poseidon::k_linear_hash_rows (leaf hashing, %.0f%% of the step)" % (100 * phase["leaf_ms"] / dev_ms),
                 "bound": "hbm", "achieved": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                "frac": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
-                "note": "integer-pipe bound, not HBM bound: %.3f G Poseidon permutations/s (see phases.leaf.int_pipe)" % (leaf_perm / phase["leaf_ms"] / 1e6)}
+                "frac": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9 / hbm_peak, "traffic": leaf_bytes * TRAFFIC_RATIO,
+                "traffic_source": "dram__bytes_read+write of the same kernel captured with ncu --set full on the 2^21 x 256 shape (profiles/r1_07_leaf_ncu.txt), scaled by bytes",
+                "peak_source": peak_src,
+                "note": "the kernel is bound by integer instruction issue, not HBM: %.3f G Poseidon permutations/s = %.2f warp instr/clk/SMSP "
+                        "(ncu: 19.06 k instr per permutation, fmaheavy pipe 83%% busy); the measured issue cost model of DESIGN.md 4 "
+                        "(2 clk per IMAD/LOP/SHF, 1-1.5 per IADD3) caps this mix at 0.57" % (leaf_perm / phase["leaf_ms"] / 1e6, ipc),
+                "issue": {"warp_instr_per_clk_per_smsp": ipc, "model_cap": 0.57, "frac_of_model": ipc / 0.57}}
+    epasses = (n * (1 if logn <= 8 else (logn + 7) // 8) + e * (1 if loge <= 8 else (loge + 7) // 8)) * ncols
     phases = {
-        "lde": {"ms": phase["lde_ms"], "kernels": "ntt::k_pass x %d passes per column block" % lde_passes, "bound": "hbm",
+        "lde": {"ms": phase["lde_ms"], "kernels": "ntt::k_pass x %d passes per column block" % lde_passes, "bound": "integer issue, then hbm",
                 "algorithmic_bytes": lde_bytes, "achieved_GBps": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9,
-                "frac": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9 / hbm_peak},
+                "frac": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9 / hbm_peak, "element_passes": epasses,
+                "ns_per_element_pass": phase["lde_ms"] * 1e6 / epasses},
         "leaf": {"ms": phase["leaf_ms"], "permutations": leaf_perm, "Gperm_per_s": leaf_perm / phase["leaf_ms"] / 1e6},
         "tree": {"ms": phase["tree_ms"], "permutations": tree_perm, "Gperm_per_s": tree_perm / max(phase["tree_ms"], 1e-9) / 1e6},
     }
@@ -289,7 +301,7 @@ def main():
             assert np.array_equal(root2, root), "e2e root differs from the device-resident root"
             e2e = {"value": e * ncols / float(np.mean(ts)), "unit": "ext-elem/s", "ms_per_step": float(np.mean(ts)) * 1e3,
                    "h2d_bytes_per_step": in_b, "d2h_bytes_per_step": lde_b + tree_b + 32, "steps": e2e_steps,
-                   "call": "gl_commit_host(lde_out, tree_out, in, E, N, ncols, root) with cudaHostAlloc'ed buffers"}
+                   "call": "gl_commit_host(lde_out, tree_out, in, E, N, ncols, root) with cudaHostAlloc'ed buffers: column-block H2D / LDE / D2H pipeline, hashing overlaps the download"}
         except Exception as ex:  # not enough pinned host memory on this box etc.
             e2e = {"value": None, "unit": "ext-elem/s", "error": str(ex)[:200], "h2d_bytes_per_step": in_b, "d2h_bytes_per_step": lde_b + tree_b + 32}
         finally:

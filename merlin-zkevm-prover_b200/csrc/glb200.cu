@@ -511,7 +511,14 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         TRY(arena_reserve((size_t)(n + n_ext) * cb * 8));
         TRY(stage.alloc((size_t)2 * n * cb * 8));
         u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cb;
-        const u64 nb = (ncols + cb - 1) / cb;
+        // block boundaries: a narrow first block so that compute starts after a short upload, then full-width blocks
+        std::vector<u64> starts;
+        for (u64 c0 = 0; c0 < ncols;) {
+            starts.push_back(c0);
+            c0 += (c0 == 0 && ncols > 2 * cb) ? 32 : ((c0 == 32 && ncols > 2 * cb) ? cb - 32 : cb);
+        }
+        starts.push_back(ncols);
+        const u64 nb = starts.size() - 1;
         std::vector<cudaEvent_t> ev_in(nb), ev_done(nb);
         for (u64 k = 0; k < nb; k++) {
             CU(cudaEventCreateWithFlags(&ev_in[k], cudaEventDisableTiming));
@@ -519,8 +526,8 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         }
         int rc = GL_OK;
         for (u64 k = 0; k < nb && rc == GL_OK; k++) {
-            const u64 c0 = k * cb;
-            const u32 w = (u32)((ncols - c0 < cb) ? ncols - c0 : cb);
+            const u64 c0 = starts[k];
+            const u32 w = (u32)(starts[k + 1] - c0);
             u64 *st = (u64 *)stage.p + (k & 1) * (size_t)n * cb;
             if (k >= 2) cudaStreamWaitEvent(g.s_h2d, ev_done[k - 2], 0); // staging buffer free again
             cudaMemcpy2DAsync(st, cb * 8, in + c0, ncols * 8, (size_t)w * 8, n, cudaMemcpyHostToDevice, g.s_h2d);
@@ -529,6 +536,10 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
             rc = run_ntt(coef, cb, st, cb, tmp, cb, logn, w, true, 2, n);
             if (rc == GL_OK) rc = run_ntt(lde + c0, ncols, coef, cb, tmp, cb, loge, w, false, 0, n);
             cudaEventRecord(ev_done[k], g.stream);
+            if (do_tree && ncols > 4 && rc == GL_OK) { // hash this block's columns now; the capacity words wait in the leaf slots
+                poseidon::k_linear_hash_partial<<<poseidon::grid_for(n_ext), poseidon::kThreads, 0, g.stream>>>((u64 *)t.p, lde, n_ext, ncols, (u32)c0, w);
+                g.launches++;
+            }
             if (lde_out) {
                 cudaStreamWaitEvent(g.s_d2h, ev_done[k], 0);
                 cudaMemcpy2DAsync(lde_out + c0, ncols * 8, lde + c0, ncols * 8, (size_t)w * 8, n_ext, cudaMemcpyDeviceToHost, g.s_d2h);
@@ -544,7 +555,12 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         for (u64 k = 0; k < nb; k++) { cudaEventDestroy(ev_in[k]); cudaEventDestroy(ev_done[k]); } // released when complete
     }
     if (do_tree) {
-        TRY(merkletree_dev((u64 *)t.p, lde, ncols, n_ext, false));
+        if (ncols > 4) { // leaves were hashed block by block above
+            g.launches += poseidon::launch_tree_levels((u64 *)t.p, n_ext, g.stream);
+            CU(cudaGetLastError());
+        } else {
+            TRY(merkletree_dev((u64 *)t.p, lde, ncols, n_ext, false));
+        }
         const u64 tw = gl_tree_num_elements(n_ext);
         if (tree_out) CU(cudaMemcpyAsync(tree_out, t.p, tw * 8, cudaMemcpyDeviceToHost, g.stream));
         if (root) CU(cudaMemcpyAsync(root, (u64 *)t.p + tw - 4, 32, cudaMemcpyDeviceToHost, g.stream));

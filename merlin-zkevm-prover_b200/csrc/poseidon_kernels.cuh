@@ -83,6 +83,40 @@ __global__ void __launch_bounds__(kThreads) k_linear_hash_rows(u64 *__restrict__
     linear_hash_row<PANELS>(digests + row * 4, rp, PANELS ? nullptr : rp.base[0] + row * ncols, row, ncols);
 }
 
+// The same sponge, one column block at a time: absorbs columns [c0, c0 + w) of every row (c0 a multiple of 8; w a
+// multiple of 8 unless this is the last block) and keeps the running capacity words state[0..4) in the row's digest
+// slot between blocks.  After the block with c0 + w == ncols_total the slot holds the leaf digest.  Lets the
+// pipelined host-pointer commit hash block k while block k+1 is uploaded and transformed.  Needs ncols_total > 4.
+__global__ void __launch_bounds__(kThreads) k_linear_hash_partial(u64 *__restrict__ digests, const u64 *__restrict__ src, u64 nrows, u64 pitch,
+                                                                  u32 c0, u32 w)
+{
+    u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    const u64 *p = src + row * pitch + c0;
+    u64 *d = digests + row * 4;
+    u64 s[12];
+#pragma unroll
+    for (int i = 0; i < 4; i++) s[8 + i] = c0 ? d[i] : 0;
+    const u32 full = w >> 3;
+    for (u32 c = 0; c < full; c++) {
+#pragma unroll
+        for (u32 i = 0; i < 8; i++) s[i] = p[c * 8 + i];
+        permute<true>(s);
+#pragma unroll
+        for (int i = 0; i < 4; i++) s[8 + i] = s[i];
+    }
+    const u32 rem = w & 7;
+    if (rem) {
+#pragma unroll
+        for (u32 i = 0; i < 8; i++) s[i] = i < rem ? p[full * 8 + i] : 0;
+        permute<true>(s);
+#pragma unroll
+        for (int i = 0; i < 4; i++) s[8 + i] = s[i];
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) d[i] = gl::canon(s[8 + i]);
+}
+
 // merkletree_batch (poseidon_goldilocks.cpp:113-164, 302-352): digest of every `batch`-column slice of every
 // row; thread v = (row, slice).  The per-row digest of these digests is a k_linear_hash_rows over the result.
 __global__ void __launch_bounds__(kThreads) k_linear_hash_batches(u64 *__restrict__ out, const u64 *__restrict__ src, u64 nrows, u32 ncols,
