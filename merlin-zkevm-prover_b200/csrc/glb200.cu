@@ -513,9 +513,10 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cb;
         // block boundaries: a narrow first block so that compute starts after a short upload, then full-width blocks
         std::vector<u64> starts;
+        const bool graded = cb > 32 && ncols > 2 * cb;
         for (u64 c0 = 0; c0 < ncols;) {
             starts.push_back(c0);
-            c0 += (c0 == 0 && ncols > 2 * cb) ? 32 : ((c0 == 32 && ncols > 2 * cb) ? cb - 32 : cb);
+            c0 += (graded && c0 == 0) ? 32 : ((graded && c0 == 32) ? cb - 32 : cb);
         }
         starts.push_back(ncols);
         const u64 nb = starts.size() - 1;

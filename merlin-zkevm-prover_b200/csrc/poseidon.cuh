@@ -35,6 +35,8 @@ __constant__ u64 c_RCP[22];          // partial-round constants C[60..82)
 __constant__ uint4 c_PL[12 * 12];    // dense layer: limbs of P[j][i] at [i*12 + j] (x,y,z; w unused)
 __constant__ uint4 c_SL[22 * 12];    // partial round r: limbs of the dot row S[23r + i] at [r*12 + i]
 __constant__ u64 c_SV[22 * 11];      // partial round r: rank-1 column S[23r + 12 + i], i < 11
+__constant__ double4 c_PLd[12 * 12]; // the same dense-layer / dot-row constants as four 16-bit limbs held as doubles
+__constant__ double4 c_SLd[22 * 12];
 
 // MDS circulant (reference M[j][i] = circ[(i-j) mod 12] + 8*[i==j==0]) as immediates.
 __device__ __forceinline__ constexpr u32 mds_entry(int j, int i)
@@ -54,9 +56,84 @@ __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
 
 // new[i] = sum_j M[j][i] old[j]  (poseidon_goldilocks.hpp:148-162).  Entries < 64, so the sums of
 // the low and of the high 32-bit halves each fit 64 bits (< 2^42); one 96-bit reduction per output.
+//
+// The 24 multiply-adds per output run on the FP64 pipe, which issues beside the integer pipe on this SM
+// (profiles/r1_09_ubench_fp64.txt: DFMA + IMAD.WIDE pairs issue in the time of one): a 32-bit half h is the
+// double (2^52 + h) - 2^52 (register pairing + one DADD), every partial sum 2^52 + sum m*h is an integer
+// below 2^53 and therefore exact, and the low 52 bits of the final double ARE the integer sum.
+__device__ __forceinline__ double u32_to_f64(u32 h) { return __hiloint2double(0x43300000, (int)h) - 4503599627370496.0; }
+
+constexpr double kTwo52 = 4503599627370496.0;
+constexpr u64 kTwo52Bits = 0x4330000000000000ULL;
+// -(x) mod p for a 128-bit x (compile time)
+constexpr u64 neg_mod_p(unsigned __int128 x) { return (u64)((gl::P - (u64)(x % gl::P)) % gl::P); }
+
+// Lazy dot product on the FP64 pipe: sum of up to 12 products a*c, a any u64 (as two exact doubles a0, a1 < 2^32),
+// c a constant given as four 16-bit limbs held as doubles.  Eight columns col[h][l] of weight 2^(32h+16l); every
+// partial sum is 2^52 + (an integer < 2^52) and therefore exact.  The 2^52 biases are never masked off: the
+// starting values of the h = 0 columns carry 16-bit offsets d_l with  sum_l d_l 2^(16l) = -(bias total) mod p,
+// so the RAW bit patterns of the eight doubles already sum to the dot product mod p.
+struct DotF {
+    double c0[4], c1[4];
+    __device__ __forceinline__ void init()
+    {
+        // bias total = kTwo52Bits * sum_{h,l} 2^(32h+16l)
+        constexpr unsigned __int128 W = ((unsigned __int128)1 + ((unsigned __int128)1 << 16) + ((unsigned __int128)1 << 32) + ((unsigned __int128)1 << 48)) *
+                                        (((unsigned __int128)1 << 32) + 1);
+        constexpr u64 D = neg_mod_p((unsigned __int128)(kTwo52Bits % gl::P) * (W % gl::P));
+#pragma unroll
+        for (int l = 0; l < 4; l++) {
+            c0[l] = kTwo52 + (double)((D >> (16 * l)) & 0xFFFF);
+            c1[l] = kTwo52;
+        }
+    }
+    __device__ __forceinline__ void mad(double a0, double a1, const double4 &k)
+    {
+        c0[0] = fma(a0, k.x, c0[0]); c0[1] = fma(a0, k.y, c0[1]); c0[2] = fma(a0, k.z, c0[2]); c0[3] = fma(a0, k.w, c0[3]);
+        c1[0] = fma(a1, k.x, c1[0]); c1[1] = fma(a1, k.y, c1[1]); c1[2] = fma(a1, k.z, c1[2]); c1[3] = fma(a1, k.w, c1[3]);
+    }
+    __device__ __forceinline__ u64 fold() const
+    {
+        typedef unsigned __int128 w128;
+        const w128 i0 = (w128)(u64)__double_as_longlong(c0[0]) + ((w128)(u64)__double_as_longlong(c0[1]) << 16) +
+                        ((w128)(u64)__double_as_longlong(c0[2]) << 32) + ((w128)(u64)__double_as_longlong(c0[3]) << 48);
+        const w128 i1 = (w128)(u64)__double_as_longlong(c1[0]) + ((w128)(u64)__double_as_longlong(c1[1]) << 16) +
+                        ((w128)(u64)__double_as_longlong(c1[2]) << 32) + ((w128)(u64)__double_as_longlong(c1[3]) << 48);
+        // i0, i1 < 2^112; i0 + i1 2^32 < 2^145: five words, the top one < 2^17
+        const u64 lo = (u64)i0, hi = (u64)(i0 >> 64), l1 = (u64)i1, h1 = (u64)(i1 >> 64);
+        u32 x0 = (u32)lo, x1 = (u32)(lo >> 32), x2 = (u32)hi, x3 = (u32)(hi >> 32), x4;
+        asm("add.cc.u32 %0, %0, %4;\n\taddc.cc.u32 %1, %1, %5;\n\taddc.cc.u32 %2, %2, %6;\n\taddc.u32 %3, %7, 0;"
+            : "+r"(x1), "+r"(x2), "+r"(x3), "=r"(x4)
+            : "r"((u32)l1), "r"((u32)(l1 >> 32)), "r"((u32)h1), "r"((u32)(h1 >> 32)));
+        return gl::reduce160(x0, x1, x2, x3, x4);
+    }
+};
+
 template <int NOUT = 12>
 __device__ __forceinline__ void mds_layer(u64 (&s)[12])
 {
+#ifndef GLB_MDS_INT
+    // bias of the two sums, value L + H 2^32: kTwo52Bits (1 + 2^32); cancelled by 32-bit offsets in the starting values
+    constexpr u64 DM = neg_mod_p((unsigned __int128)(kTwo52Bits % gl::P) * (((u64)1 << 32) + 1));
+    double lo[12], hi[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++) {
+        lo[j] = u32_to_f64((u32)s[j]);
+        hi[j] = u32_to_f64((u32)(s[j] >> 32));
+    }
+#pragma unroll
+    for (int i = 0; i < NOUT; i++) {
+        double dl = kTwo52 + (double)(DM & 0xFFFFFFFFu), dh = kTwo52 + (double)(DM >> 32);
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            dl = fma((double)mds_entry(j, i), lo[j], dl);
+            dh = fma((double)mds_entry(j, i), hi[j], dh);
+        }
+        const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh); // raw: bias included
+        const u64 t = (L >> 32) + H; // < 2^64
+        s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+    }
+#else
     u32 lo[12], hi[12];
 #pragma unroll
     for (int j = 0; j < 12; j++) {
@@ -74,16 +151,32 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
         u64 t = (L >> 32) + H; // < 2^43
         s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
     }
+#endif
 }
 
 // Dense layer before the partial rounds: new[i] = sum_j P[j][i] old[j]   (poseidon_goldilocks.cpp:17)
 __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 {
+#ifndef GLB_DOT_INT
+    double o0[12], o1[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++) {
+        o0[j] = u32_to_f64((u32)s[j]);
+        o1[j] = u32_to_f64((u32)(s[j] >> 32));
+    }
+#else
     u64 o[12];
 #pragma unroll
     for (int j = 0; j < 12; j++) o[j] = s[j];
+#endif
 #pragma unroll 1
     for (int i = 0; i < 12; i++) {
+#ifndef GLB_DOT_INT
+        DotF d;
+        d.init();
+#pragma unroll
+        for (int j = 0; j < 12; j++) d.mad(o0[j], o1[j], c_PLd[i * 12 + j]);
+#else
         gl::Dot d;
         d.zero();
 #pragma unroll
@@ -91,6 +184,7 @@ __device__ __forceinline__ void dense_layer(u64 (&s)[12])
             const uint4 l = c_PL[i * 12 + j];
             d.mad(o[j], l.x, l.y, l.z);
         }
+#endif
         const u64 acc = d.fold();
         // rotate instead of indexing registers dynamically: after 12 steps s[] holds new[0..12)
         s[0] = s[1]; s[1] = s[2]; s[2] = s[3]; s[3] = s[4]; s[4] = s[5]; s[5] = s[6];
@@ -105,6 +199,14 @@ __device__ __forceinline__ void partial_rounds(u64 (&s)[12])
 #pragma unroll 1
     for (int r = 0; r < 22; r++) {
         const u64 t = sbox_add(s[0], c_RCP[r]);
+#ifndef GLB_DOT_INT
+        DotF d;
+        d.init();
+        d.c0[0] = fma(25.0, u32_to_f64((u32)t), d.c0[0]); // S[23r] == 25 in every round (checked when the tables are built)
+        d.c1[0] = fma(25.0, u32_to_f64((u32)(t >> 32)), d.c1[0]);
+#pragma unroll
+        for (int i = 1; i < 12; i++) d.mad(u32_to_f64((u32)s[i]), u32_to_f64((u32)(s[i] >> 32)), c_SLd[r * 12 + i]);
+#else
         gl::Dot d;
         d.zero();
         gl::madw(d.c00, (u32)t, 25u); // S[23r] == 25 in every round (checked when the tables are built)
@@ -114,6 +216,7 @@ __device__ __forceinline__ void partial_rounds(u64 (&s)[12])
             const uint4 l = c_SL[r * 12 + i];
             d.mad(s[i], l.x, l.y, l.z);
         }
+#endif
 #pragma unroll
         for (int i = 1; i < 12; i++) s[i] = gl::mad(t, c_SV[r * 11 + i - 1], s[i]);
         s[0] = d.fold();
