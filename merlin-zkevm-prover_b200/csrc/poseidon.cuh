@@ -66,7 +66,7 @@ __device__ __forceinline__ double u32_to_f64(u32 h) { return __hiloint2double(0x
 constexpr double kTwo52 = 4503599627370496.0;
 constexpr u64 kTwo52Bits = 0x4330000000000000ULL;
 // -(x) mod p for a 128-bit x (compile time)
-constexpr u64 neg_mod_p(unsigned __int128 x) { return (u64)((gl::P - (u64)(x % gl::P)) % gl::P); }
+__host__ __device__ constexpr u64 neg_mod_p(unsigned __int128 x) { return (u64)((gl::P - (u64)(x % gl::P)) % gl::P); }
 
 // Lazy dot product on the FP64 pipe: sum of up to 12 products a*c, a any u64 (as two exact doubles a0, a1 < 2^32),
 // c a constant given as four 16-bit limbs held as doubles.  Eight columns col[h][l] of weight 2^(32h+16l); every
@@ -157,7 +157,7 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
 // Dense layer before the partial rounds: new[i] = sum_j P[j][i] old[j]   (poseidon_goldilocks.cpp:17)
 __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 {
-#ifndef GLB_DOT_INT
+#ifdef GLB_DENSE_F64
     double o0[12], o1[12];
 #pragma unroll
     for (int j = 0; j < 12; j++) {
@@ -171,7 +171,7 @@ __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 #endif
 #pragma unroll 1
     for (int i = 0; i < 12; i++) {
-#ifndef GLB_DOT_INT
+#ifdef GLB_DENSE_F64
         DotF d;
         d.init();
 #pragma unroll
@@ -199,7 +199,7 @@ __device__ __forceinline__ void partial_rounds(u64 (&s)[12])
 #pragma unroll 1
     for (int r = 0; r < 22; r++) {
         const u64 t = sbox_add(s[0], c_RCP[r]);
-#ifndef GLB_DOT_INT
+#ifdef GLB_PARTIAL_F64
         DotF d;
         d.init();
         d.c0[0] = fma(25.0, u32_to_f64((u32)t), d.c0[0]); // S[23r] == 25 in every round (checked when the tables are built)

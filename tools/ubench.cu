@@ -148,6 +148,19 @@ int main(int argc, char **argv)
         printf("perm only done\n");
         return 0;
     }
+    if (argc > 1 && !strcmp(argv[1], "leaf")) { // the leaf kernel of the library on a 2^20 x 600 matrix (75 perms per row)
+        const u64 rows = 1ULL << 20, cols = 600;
+        u64 *a, *dg;
+        CK(cudaMalloc(&a, rows * cols * 8)); CK(cudaMalloc(&dg, rows * 32));
+        CK(cudaMemset(a, 0x5A, rows * cols * 8));
+        for (int rep = 0; rep < 3; rep++) {
+            CK(cudaEventRecord(e0));
+            poseidon::launch_linear_hash_rows(dg, a, rows, cols, 0);
+            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+            printf("leaf   2^20 x 600  %8.3f ms  %8.2f M perm/s\n", time_ms(e0, e1), rows * 75.0 / time_ms(e0, e1) / 1e3);
+        }
+        return 0;
+    }
     const bool skip_mem = argc > 1 && !strcmp(argv[1], "nomem");
     // ---- 1. issue rates
     const char *names[] = {"IMAD.WIDE.U32 (mad.wide.u32)", "IMAD (mad.lo.u32)", "IADD3+IADD3.X pair (add.cc/addc)", "LOP3", "mix: 1 mad.wide + 1 add.cc/addc pair",

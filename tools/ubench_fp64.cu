@@ -7,6 +7,8 @@ typedef unsigned long long u64;
 typedef unsigned int u32;
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(1); } } while (0)
 
+__constant__ double c_k[64];
+
 template <int OP>
 __global__ void k_issue(u64 *out, int iters, u32 seed)
 {
@@ -14,9 +16,10 @@ __global__ void k_issue(u64 *out, int iters, u32 seed)
     u64 acc[8];
     double d[8];
     u32 r[8];
+    u64 acc2[8];
     const double m = 1.0 + 1e-9 * seed, c = 1e-3 * threadIdx.x;
 #pragma unroll
-    for (int i = 0; i < 8; i++) { acc[i] = a + i; d[i] = 1.0 + i; r[i] = a * (i + 1); }
+    for (int i = 0; i < 8; i++) { acc[i] = a + i; acc2[i] = b + i; d[i] = 1.0 + i; r[i] = a * (i + 1); }
     for (int it = 0; it < iters; it++) {
 #pragma unroll
         for (int rep = 0; rep < 8; rep++) {
@@ -27,6 +30,18 @@ __global__ void k_issue(u64 *out, int iters, u32 seed)
                 if (OP == 3) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(b), "r"(a));
                 if (OP == 4) asm volatile("add.cc.u32 %0, %0, %1;\n\taddc.u32 %0, %0, %2;" : "+r"(r[i]) : "r"(a), "r"(b));
                 if (OP == 5) asm volatile("add.rn.f64 %0, %0, %1;" : "+d"(d[i]) : "d"(c));
+                if (OP >= 7 && OP <= 11) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[i]) : "d"(m), "d"(c));
+                if (OP == 9) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[(i + 4) & 7]) : "d"(c), "d"(m));
+                if (OP >= 7 && OP <= 11) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a), "r"(b));
+                if (OP == 7 || OP == 11) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc2[i]) : "r"(b), "r"(a));
+                if (OP == 11) {
+                    asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[(i + 4) & 7]) : "r"(a), "r"(a));
+                    asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc2[(i + 4) & 7]) : "r"(b), "r"(b));
+                }
+                if (OP == 8) asm volatile("add.u32 %0, %0, %1;" : "+r"(r[i]) : "r"(b));
+                if (OP == 10) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(r[i]) : "r"(a), "r"(b));
+                if (OP == 12 || OP == 13) d[i] = fma(d[i], c_k[(it * 8 + i) & 63], c); // constant through a uniform register (LDCU)
+                if (OP == 13) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a), "r"(b));
                 if (OP == 6) { // DADD + LOP3
                     asm volatile("add.rn.f64 %0, %0, %1;" : "+d"(d[i]) : "d"(c));
                     asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(r[i]) : "r"(a), "r"(b));
@@ -36,7 +51,7 @@ __global__ void k_issue(u64 *out, int iters, u32 seed)
     }
     u64 t = 0;
 #pragma unroll
-    for (int i = 0; i < 8; i++) t += acc[i] + (u64)__double_as_longlong(d[i]) + r[i];
+    for (int i = 0; i < 8; i++) t += acc[i] + acc2[i] + (u64)__double_as_longlong(d[i]) + r[i];
     out[blockIdx.x * blockDim.x + threadIdx.x] = t + a;
 }
 
@@ -46,13 +61,15 @@ int main()
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, 0));
     const int sms = prop.multiProcessorCount;
+    { double hk[64]; for (int i = 0; i < 64; i++) hk[i] = 1.0 + 1e-12 * i; CK(cudaMemcpyToSymbol(c_k, hk, sizeof hk)); }
     u64 *out;
     CK(cudaMalloc(&out, (size_t)sms * 16 * 1024 * 8));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-    const char *names[] = {"DFMA", "IMAD.WIDE", "1 DFMA + 1 IMAD.WIDE", "1 DFMA + 2 IMAD.WIDE", "1 DFMA + 1 IMAD.WIDE + IADD3 pair", "DADD", "1 DADD + 1 LOP3"};
-    const int per[] = {1, 1, 2, 3, 4, 1, 2};
-    for (int op = 0; op < 7; op++)
+    const char *names[] = {"DFMA", "IMAD.WIDE", "1 DFMA + 1 IMAD.WIDE", "1 DFMA + 2 IMAD.WIDE", "1 DFMA + 1 IMAD.WIDE + IADD3 pair", "DADD", "1 DADD + 1 LOP3",
+                           "1 DFMA + 2 independent IMAD.WIDE", "1 DFMA + 1 IMAD.WIDE + 1 IADD3", "2 DFMA + 1 IMAD.WIDE", "1 DFMA + 1 IMAD.WIDE + 1 LOP3", "1 DFMA + 4 independent IMAD.WIDE", "DFMA with LDCU constant operand", "DFMA(LDCU const) + IMAD.WIDE"};
+    const int per[] = {1, 1, 2, 3, 4, 1, 2, 3, 3, 3, 3, 5, 1, 2};
+    for (int op = 0; op < 14; op++)
         for (int warps = 8; warps <= 32; warps *= 2) {
             int blocks = sms * 2, threads = warps * 32 / 2, iters = 2000;
             float ms = 0;
@@ -66,6 +83,13 @@ int main()
                 case 4: k_issue<4><<<blocks, threads>>>(out, iters, 12345); break;
                 case 5: k_issue<5><<<blocks, threads>>>(out, iters, 12345); break;
                 case 6: k_issue<6><<<blocks, threads>>>(out, iters, 12345); break;
+                case 7: k_issue<7><<<blocks, threads>>>(out, iters, 12345); break;
+                case 8: k_issue<8><<<blocks, threads>>>(out, iters, 12345); break;
+                case 9: k_issue<9><<<blocks, threads>>>(out, iters, 12345); break;
+                case 10: k_issue<10><<<blocks, threads>>>(out, iters, 12345); break;
+                case 11: k_issue<11><<<blocks, threads>>>(out, iters, 12345); break;
+                case 12: k_issue<12><<<blocks, threads>>>(out, iters, 12345); break;
+                case 13: k_issue<13><<<blocks, threads>>>(out, iters, 12345); break;
                 }
                 CK(cudaEventRecord(e1));
                 CK(cudaEventSynchronize(e1));
