@@ -10,8 +10,10 @@
 namespace poseidon {
 
 constexpr int kThreads = 128;
+// 4 CTAs of 128 threads per SM (<= 128 registers): the permutation with the FP64 MDS needs ~120 registers to stay spill-free;
+// tools/ubench leaf: 1023 M perm/s against 1005 (5 CTAs, 96 registers, spills) and 992 (6 CTAs)
 #ifndef GLB_LEAF_MINBLOCKS
-#define GLB_LEAF_MINBLOCKS 1
+#define GLB_LEAF_MINBLOCKS 4
 #endif
 
 __global__ void __launch_bounds__(kThreads) k_hash_full_result(u64 *__restrict__ out, const u64 *__restrict__ in, u64 n)
@@ -90,7 +92,7 @@ __global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_linear_hash_ro
 // multiple of 8 unless this is the last block) and keeps the running capacity words state[0..4) in the row's digest
 // slot between blocks.  After the block with c0 + w == ncols_total the slot holds the leaf digest.  Lets the
 // pipelined host-pointer commit hash block k while block k+1 is uploaded and transformed.  Needs ncols_total > 4.
-__global__ void __launch_bounds__(kThreads) k_linear_hash_partial(u64 *__restrict__ digests, const u64 *__restrict__ src, u64 nrows, u64 pitch,
+__global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_linear_hash_partial(u64 *__restrict__ digests, const u64 *__restrict__ src, u64 nrows, u64 pitch,
                                                                   u32 c0, u32 w)
 {
     u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -134,7 +136,7 @@ __global__ void __launch_bounds__(kThreads) k_linear_hash_batches(u64 *__restric
     linear_hash_row<false>(out + v * 4, rp, src + row * ncols + (u64)j * batch, 0, len);
 }
 
-__global__ void __launch_bounds__(kThreads) k_tree_level(u64 *__restrict__ parents, const u64 *__restrict__ children, u64 nparents)
+__global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_tree_level(u64 *__restrict__ parents, const u64 *__restrict__ children, u64 nparents)
 {
     u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= nparents) return;
