@@ -199,6 +199,8 @@ def main():
     glb = ge.load()
     dist = None
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "NONE"  # keeps NCCL's version banner off stdout: rank 0 prints exactly one JSON line
         import torch
         import torch.distributed as dist_
         dist = dist_

@@ -80,10 +80,7 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
             for i in range(1 + max(1, min(args.steps, 3))):
                 barrier()
                 t1 = time.perf_counter()
-                L.gl_h2d(C.c_void_p(din.ptr), hin, in_b)
-                r2 = glb.commit_mgpu(dlde.ptr, dpan.ptr, dsub.ptr, din.ptr, e, n, ncols)
-                L.gl_d2h(hrows, C.c_void_p(dpan.ptr), rows_b)
-                L.gl_d2h(hsub, C.c_void_p(dsub.ptr), sub_b)
+                r2 = glb.commit_mgpu_host(hrows.value, hsub.value, hin.value, dlde.ptr, dpan.ptr, dsub.ptr, e, n, ncols)
                 barrier()
                 if i > 0:
                     ts.append(time.perf_counter() - t1)
@@ -92,7 +89,7 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
             e2e = {"value": e * ncols / float(te.item()), "unit": "ext-elem/s", "ms_per_step": float(te.item()) * 1e3,
                    "h2d_bytes_per_step": n * ncols * 8, "d2h_bytes_per_step": e * ncols * 8 + world * sub_b + 32,
-                   "call": "per rank: gl_h2d(column block) + gl_commit_mgpu + gl_d2h(row block, subtree); pinned host buffers; bytes summed over ranks"}
+                   "call": "per rank: gl_commit_mgpu_host(row panels out, subtree out, column block in): sub-block upload overlaps the LDE, panel download overlaps the leaf hashing; pinned host buffers; bytes summed over ranks"}
         except Exception as ex:
             e2e = {"value": None, "unit": "ext-elem/s", "error": str(ex)[:200], "h2d_bytes_per_step": n * ncols * 8, "d2h_bytes_per_step": e * ncols * 8}
         finally:

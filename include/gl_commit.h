@@ -170,6 +170,14 @@ uint64_t gl_mgpu_col_start(uint64_t ncols, int world, int rank);
  * subtree: (2*n_ext/world - 1)*4 words (out); root: HOST pointer, 4 words (same on every rank). */
 int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, const uint64_t *in_cols,
                    uint64_t n_ext, uint64_t n, uint64_t ncols_total, uint64_t root[4]);
+/* The same with HOST input and output (what a Starks caller that keeps the trace in host memory uses,
+ * starks.cpp:52-56): in_cols_host is this rank's n x w column block (row-major, pitch w); row_panels_host
+ * receives the rank's row panels and subtree_host its subtree (either may be NULL).  The upload of column
+ * sub-block k+1 overlaps the LDE of sub-block k, and the download of the panels overlaps the leaf hashing.
+ * lde_cols / row_panels / subtree are caller-owned DEVICE work buffers of the sizes gl_commit_mgpu needs. */
+int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const uint64_t *in_cols_host,
+                        uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, uint64_t n_ext, uint64_t n,
+                        uint64_t ncols_total, uint64_t root[4]);
 /* Assemble the full (2*n_ext-1)*4-word node array (MerkleTreeGL::nodes layout) on every rank. */
 int gl_mgpu_gather_tree(uint64_t *tree_full, const uint64_t *subtree, uint64_t n_ext);
 /* Benchmark helper: the column range [col0, col0+ncols_local) of gl_fill_synthetic_dev's matrix. */

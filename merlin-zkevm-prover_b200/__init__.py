@@ -76,6 +76,7 @@ SIGNATURES = {
     "gl_mgpu_shutdown": (C.c_int, []),
     "gl_mgpu_col_start": (_u64, [_u64, C.c_int, C.c_int]),
     "gl_commit_mgpu": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64p]),
+    "gl_commit_mgpu_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64p]),
     "gl_mgpu_gather_tree": (C.c_int, [C.c_void_p, C.c_void_p, _u64]),
     "gl_fill_synthetic_cols_dev": (C.c_int, [C.c_void_p, _u64, _u64, _u64, _u64, _u64]),
 }
@@ -331,6 +332,14 @@ def commit_mgpu(lde_cols, row_panels, subtree, in_cols, n_ext, n, ncols_total):
     root = np.zeros(4, dtype=np.uint64)
     _check(lib().gl_commit_mgpu(C.c_void_p(lde_cols), C.c_void_p(row_panels), C.c_void_p(subtree), C.c_void_p(in_cols),
                                 n_ext, n, ncols_total, _p(root)))
+    return root
+
+
+def commit_mgpu_host(row_panels_host, subtree_host, in_cols_host, lde_cols, row_panels, subtree, n_ext, n, ncols_total):
+    """Host pointers (ints or None) in/out, device work buffers; pipelined upload / LDE and download / hashing."""
+    root = np.zeros(4, dtype=np.uint64)
+    _check(lib().gl_commit_mgpu_host(C.c_void_p(row_panels_host), C.c_void_p(subtree_host), C.c_void_p(in_cols_host), C.c_void_p(lde_cols),
+                                     C.c_void_p(row_panels), C.c_void_p(subtree), n_ext, n, ncols_total, _p(root)))
     return root
 
 

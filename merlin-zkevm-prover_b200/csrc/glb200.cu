@@ -1003,6 +1003,105 @@ int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, 
     return GL_OK;
 }
 
+// Host-pointer variant of gl_commit_mgpu, pipelined: the rank's column block is uploaded one column sub-block at a
+// time while the previous sub-block is being extended; after the exchange the received row panels are downloaded on
+// the copy stream WHILE the leaves are hashed and the subtree is built; the subtree follows.  Device buffers as for
+// gl_commit_mgpu (caller-owned work space); host buffers should be pinned.
+int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const uint64_t *in_cols_host, uint64_t *lde_cols,
+                        uint64_t *row_panels, uint64_t *subtree, uint64_t n_ext, uint64_t n, uint64_t ncols_total, uint64_t root[4])
+{
+    TRY(need_ctx());
+    if (!nc.comm) return fail(GL_ERR_ARG, "gl_commit_mgpu_host: call gl_mgpu_init first");
+    const int G = nc.world, me = nc.rank;
+    if (n == 0 || n_ext == 0 || !is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "commit: bad domain %llu -> %llu", (u64)n, (u64)n_ext);
+    if (n_ext < (u64)G) return fail(GL_ERR_ARG, "commit: %llu extended rows cannot be split over %d ranks", (u64)n_ext, G);
+    const u64 rows = n_ext / G;
+    const u64 c0r = col_start(ncols_total, G, me), w = col_start(ncols_total, G, me + 1) - c0r;
+    const u32 logn = ilog2(n), loge = ilog2(n_ext);
+
+    CU(cudaEventRecord(g.ev[0], g.stream));
+    DevBuf stage;
+    if (w) {
+        u64 cb = ((w + 3) / 4 + 31) / 32 * 32; // >= 4 sub-blocks when there are enough columns, <= 128 columns each
+        if (cb > 128) cb = 128;
+        size_t free_b = 0, total_b = 0;
+        CU(cudaMemGetInfo(&free_b, &total_b));
+        free_b += g.arena_bytes;
+        const size_t per_col = (size_t)(3 * n + n_ext) * 8; // coef + pass scratch + two staging buffers
+        while (cb > 32 && per_col * cb + ((size_t)1 << 30) > free_b) cb -= 32;
+        if (cb > w) cb = w;
+        TRY(arena_reserve((size_t)(n + n_ext) * cb * 8));
+        TRY(stage.alloc((size_t)2 * n * cb * 8));
+        u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cb;
+        const u64 nb = (w + cb - 1) / cb;
+        std::vector<cudaEvent_t> ev_in(nb), ev_done(nb);
+        for (u64 k = 0; k < nb; k++) {
+            CU(cudaEventCreateWithFlags(&ev_in[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
+        }
+        int rc = GL_OK;
+        for (u64 k = 0; k < nb && rc == GL_OK; k++) {
+            const u64 c0 = k * cb;
+            const u32 ww = (u32)((w - c0 < cb) ? w - c0 : cb);
+            u64 *st = (u64 *)stage.p + (k & 1) * (size_t)n * cb;
+            if (k >= 2) cudaStreamWaitEvent(g.s_h2d, ev_done[k - 2], 0); // staging buffer free again
+            cudaMemcpy2DAsync(st, cb * 8, in_cols_host + c0, w * 8, (size_t)ww * 8, n, cudaMemcpyHostToDevice, g.s_h2d);
+            cudaEventRecord(ev_in[k], g.s_h2d);
+            cudaStreamWaitEvent(g.stream, ev_in[k], 0);
+            rc = run_ntt(coef, cb, st, cb, tmp, cb, logn, ww, true, 2, n);
+            if (rc == GL_OK) rc = run_ntt((u64 *)lde_cols + c0, w, coef, cb, tmp, cb, loge, ww, false, 0, n);
+            cudaEventRecord(ev_done[k], g.stream);
+        }
+        cudaError_t e = cudaGetLastError();
+        for (u64 k = 0; k < nb; k++) { cudaEventDestroy(ev_in[k]); cudaEventDestroy(ev_done[k]); } // released when complete
+        if (rc == GL_OK && e != cudaSuccess) rc = fail(GL_ERR_CUDA, "pipelined multi-GPU commit: %s", cudaGetErrorString(e));
+        if (rc != GL_OK) {
+            cudaDeviceSynchronize();
+            return rc;
+        }
+    }
+    CU(cudaEventRecord(g.ev[4], g.stream));
+
+    // all-to-all, as in gl_commit_mgpu
+    poseidon::RowPanels rp = {};
+    rp.npanels = (u32)G;
+    for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
+    for (int p = 0; p < G; p++) rp.base[p] = (const u64 *)row_panels + rows * rp.start[p];
+    NC(nc.GroupStart());
+    for (int p = 0; p < G; p++) {
+        if (p == me) continue;
+        const u64 wp = rp.start[p + 1] - rp.start[p];
+        if (w) NC(nc.Send((const u64 *)lde_cols + (u64)p * rows * w, rows * w, ncclUint64, p, nc.comm, g.stream));
+        if (wp) NC(nc.Recv((void *)rp.base[p], rows * wp, ncclUint64, p, nc.comm, g.stream));
+    }
+    NC(nc.GroupEnd());
+    if (w) CU(cudaMemcpyAsync((void *)rp.base[me], (const u64 *)lde_cols + (u64)me * rows * w, rows * w * 8, cudaMemcpyDeviceToDevice, g.stream));
+    CU(cudaEventRecord(g.ev[1], g.stream));
+
+    // the panels leave for the host while they are being hashed
+    if (row_panels_host) {
+        CU(cudaStreamWaitEvent(g.s_d2h, g.ev[1], 0));
+        CU(cudaMemcpyAsync(row_panels_host, row_panels, rows * ncols_total * 8, cudaMemcpyDeviceToHost, g.s_d2h));
+    }
+    poseidon::launch_linear_hash_panels((u64 *)subtree, rp, rows, g.stream);
+    g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(g.ev[2], g.stream));
+    g.launches += poseidon::launch_tree_levels((u64 *)subtree, rows, g.stream);
+    CU(cudaGetLastError());
+    TRY(mgpu_top((const u64 *)subtree + gl_tree_num_elements(rows) - 4, root));
+    CU(cudaEventRecord(g.ev[3], g.stream));
+    if (subtree_host) CU(cudaMemcpyAsync(subtree_host, subtree, gl_tree_num_elements(rows) * 8, cudaMemcpyDeviceToHost, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    CU(cudaStreamSynchronize(g.s_d2h));
+    CU(cudaStreamSynchronize(g.s_h2d));
+    CU(cudaEventElapsedTime(&g.ms[0], g.ev[0], g.ev[4]));
+    CU(cudaEventElapsedTime(&g.ms[3], g.ev[4], g.ev[1]));
+    CU(cudaEventElapsedTime(&g.ms[1], g.ev[1], g.ev[2]));
+    CU(cudaEventElapsedTime(&g.ms[2], g.ev[2], g.ev[3]));
+    return GL_OK;
+}
+
 int gl_mgpu_gather_tree(uint64_t *tree_full, const uint64_t *subtree, uint64_t n_ext)
 {
     TRY(need_ctx());

@@ -104,6 +104,18 @@ def main():
                 assert np.array_equal(pan[off:off + rows * pw].reshape(rows, pw), lde_full[r0:r1, pc0:pc0 + pw])
             glb.mgpu_gather_tree(dfull.ptr, dsub.ptr, e)
             assert np.array_equal(dfull.download(), tree_full), "gathered tree differs"
+            # the host-pointer (pipelined) entry point must produce the same panels, subtree and root
+            sub_dev = dsub.download()
+            hin = np.ascontiguousarray(x[:, c0:c1]) if w else np.zeros(1, dtype=np.uint64)
+            hpan = np.zeros(max(1, rows * ncols), dtype=np.uint64)
+            hsub = np.zeros(glb.tree_num_elements(rows), dtype=np.uint64)
+            dlde2 = glb.DeviceBuffer(max(1, e * w))
+            dpan2 = glb.DeviceBuffer(max(1, rows * ncols))
+            dsub2 = glb.DeviceBuffer(glb.tree_num_elements(rows))
+            root2 = glb.commit_mgpu_host(hpan.ctypes.data, hsub.ctypes.data, hin.ctypes.data, dlde2.ptr, dpan2.ptr, dsub2.ptr, e, n, ncols)
+            assert np.array_equal(root2, tree_full[-4:]), "host-pointer root differs (%d,%d,%d)" % (n, e, ncols)
+            assert np.array_equal(hpan[:rows * ncols], pan), "host-pointer panels differ"
+            assert np.array_equal(hsub, sub_dev), "host-pointer subtree differs"
         dist.barrier()
     if mode == "nccl":
         glb.mgpu_shutdown()
