@@ -62,18 +62,54 @@ __device__ __forceinline__ void linear_hash_row(u64 *d, const RowPanels &rp, con
 #pragma unroll
     for (int i = 8; i < 12; i++) s[i] = 0;
     const u32 full = ncols >> 3;
-    for (u32 c = 0; c < full; c++) {
-#pragma unroll
-        for (u32 i = 0; i < 8; i++) s[i] = row_word<PANELS>(rp, p, row, c * 8 + i);
-        permute<true>(s);
-#pragma unroll
-        for (int i = 0; i < 4; i++) s[8 + i] = s[i];
-    }
     const u32 rem = ncols & 7;
-    if (rem) {
+    if (PANELS) {
+        // Stream the row panel by panel: `q` walks the current panel's copy of this row, `left` words remain in it.  A chunk
+        // that lies inside one panel is eight independent loads (the common case); only chunks that straddle a panel
+        // boundary take the word-by-word path.  All control flow is warp-uniform.
+        u32 g = 0, left = rp.start[1] - rp.start[0];
+        const u64 *q = rp.base[0] + row * left;
+        auto next_word = [&]() {
+            while (left == 0 && g + 1 < rp.npanels) {
+                g++;
+                left = rp.start[g + 1] - rp.start[g];
+                q = rp.base[g] + row * left;
+            }
+            left--;
+            return *q++;
+        };
+        for (u32 c = 0; c < full; c++) {
+            if (left >= 8) {
 #pragma unroll
-        for (u32 i = 0; i < 8; i++) s[i] = i < rem ? row_word<PANELS>(rp, p, row, full * 8 + i) : 0;
-        permute<true>(s);
+                for (u32 i = 0; i < 8; i++) s[i] = q[i];
+                q += 8;
+                left -= 8;
+            } else {
+#pragma unroll
+                for (u32 i = 0; i < 8; i++) s[i] = next_word();
+            }
+            permute<true>(s);
+#pragma unroll
+            for (int i = 0; i < 4; i++) s[8 + i] = s[i];
+        }
+        if (rem) {
+#pragma unroll
+            for (u32 i = 0; i < 8; i++) s[i] = i < rem ? next_word() : 0;
+            permute<true>(s);
+        }
+    } else {
+        for (u32 c = 0; c < full; c++) {
+#pragma unroll
+            for (u32 i = 0; i < 8; i++) s[i] = p[c * 8 + i];
+            permute<true>(s);
+#pragma unroll
+            for (int i = 0; i < 4; i++) s[8 + i] = s[i];
+        }
+        if (rem) {
+#pragma unroll
+            for (u32 i = 0; i < 8; i++) s[i] = i < rem ? p[full * 8 + i] : 0;
+            permute<true>(s);
+        }
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) d[i] = gl::canon(s[i]);
