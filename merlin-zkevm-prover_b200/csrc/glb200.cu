@@ -58,6 +58,8 @@ struct Ctx {
     int device = -1;
     cudaStream_t stream = nullptr;
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr; // copy streams of the pipelined host-pointer calls
+    cudaStream_t s_comm = nullptr;                 // multi-GPU exchange stream (row chunks overlap the leaf hashing)
+    cudaEvent_t ev_chunk[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     void *arena = nullptr;
     size_t arena_bytes = 0;
@@ -600,6 +602,8 @@ int gl_init(int device)
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g.s_comm, cudaStreamNonBlocking));
+    for (auto &e : g.ev_chunk) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : g.ev) CU(cudaEventCreate(&e));
     TRY(upload_tables());
     g.device = device;
@@ -623,7 +627,9 @@ void gl_shutdown(void)
     cudaStreamDestroy(g.stream);
     cudaStreamDestroy(g.s_h2d);
     cudaStreamDestroy(g.s_d2h);
-    g.stream = g.s_h2d = g.s_d2h = nullptr;
+    cudaStreamDestroy(g.s_comm);
+    for (auto &e : g.ev_chunk) { cudaEventDestroy(e); e = nullptr; }
+    g.stream = g.s_h2d = g.s_d2h = g.s_comm = nullptr;
     g.ready = false;
     g.device = -1;
 }
@@ -913,6 +919,61 @@ int gl_fill_synthetic_dev(uint64_t *dst, uint64_t words, uint64_t seed, uint64_t
     return GL_OK;
 }
 
+} // extern "C" (closed for the helper below)
+
+namespace {
+// Exchange + leaf hashing of the multi-GPU commit, in row chunks: chunk j of this rank's rows is exchanged on the
+// communication stream (grouped ncclSend/ncclRecv: rows [h*rows + r0, +rc) of my column block go to rank h; I receive
+// rank p's columns of my rows r0..r0+rc into panel p) while chunk j-1 is being hashed on the compute stream, so only the
+// first chunk's transfer is exposed.  Both sides of every message are contiguous (the column block and the panels are
+// row-major), so chunking needs no re-pack.  With row_panels_host the received chunk also starts its way to the host.
+// Records g.ev[1] when the first chunk has arrived and g.ev[2] after the last leaf kernel.
+int mgpu_exchange_and_hash(const u64 *lde_cols, u64 *row_panels, u64 *subtree, u64 rows, u64 w, u64 ncols_total, u64 *row_panels_host)
+{
+    const int G = nc.world, me = nc.rank;
+    poseidon::RowPanels rp = {};
+    rp.npanels = (u32)G;
+    for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
+    for (int p = 0; p < G; p++) rp.base[p] = (const u64 *)row_panels + rows * rp.start[p];
+    const u64 J = (rows % 4 == 0 && rows / 4 >= 4096) ? 4 : 1;
+    const u64 rc = rows / J;
+    CU(cudaEventRecord(g.ev[5], g.stream));
+    CU(cudaStreamWaitEvent(g.s_comm, g.ev[5], 0)); // the column block is complete
+    for (u64 j = 0; j < J; j++) {
+        const u64 r0 = j * rc;
+        NC(nc.GroupStart());
+        for (int p = 0; p < G; p++) {
+            if (p == me) continue;
+            const u64 wp = rp.start[p + 1] - rp.start[p];
+            if (w) NC(nc.Send(lde_cols + ((u64)p * rows + r0) * w, rc * w, ncclUint64, p, nc.comm, g.s_comm));
+            if (wp) NC(nc.Recv((void *)(rp.base[p] + r0 * wp), rc * wp, ncclUint64, p, nc.comm, g.s_comm));
+        }
+        NC(nc.GroupEnd());
+        if (w) CU(cudaMemcpyAsync((void *)(rp.base[me] + r0 * w), lde_cols + ((u64)me * rows + r0) * w, rc * w * 8, cudaMemcpyDeviceToDevice, g.s_comm));
+        CU(cudaEventRecord(g.ev_chunk[j], g.s_comm));
+        CU(cudaStreamWaitEvent(g.stream, g.ev_chunk[j], 0));
+        if (j == 0) CU(cudaEventRecord(g.ev[1], g.stream));
+        poseidon::RowPanels rj = rp;
+        for (int p = 0; p < G; p++) rj.base[p] = rp.base[p] + r0 * (rp.start[p + 1] - rp.start[p]);
+        poseidon::launch_linear_hash_panels(subtree + r0 * 4, rj, rc, g.stream);
+        g.launches++;
+        CU(cudaGetLastError());
+        if (row_panels_host) {
+            CU(cudaStreamWaitEvent(g.s_d2h, g.ev_chunk[j], 0));
+            for (int p = 0; p < G; p++) {
+                const u64 wp = rp.start[p + 1] - rp.start[p];
+                if (wp) CU(cudaMemcpyAsync(row_panels_host + rows * rp.start[p] + r0 * wp, rp.base[p] + r0 * wp, rc * wp * 8, cudaMemcpyDeviceToHost, g.s_d2h));
+            }
+        }
+    }
+    CU(cudaEventRecord(g.ev[2], g.stream));
+    return GL_OK;
+}
+
+} // namespace
+
+extern "C" {
+
 // ---- multi-GPU (one process per GPU) ----------------------------------------------------
 int gl_mgpu_unique_id(uint8_t id[128])
 {
@@ -971,26 +1032,7 @@ int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, 
     TRY(extend_pol_dev((u64 *)lde_cols, (const u64 *)in_cols, n_ext, n, w));
     CU(cudaEventRecord(g.ev[4], g.stream));
 
-    // all-to-all: rows [h*rows, (h+1)*rows) of my column block go to rank h; I receive rank p's columns of my rows
-    poseidon::RowPanels rp = {};
-    rp.npanels = (u32)G;
-    for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
-    for (int p = 0; p < G; p++) rp.base[p] = (const u64 *)row_panels + rows * rp.start[p];
-    NC(nc.GroupStart());
-    for (int p = 0; p < G; p++) {
-        if (p == me) continue;
-        const u64 wp = rp.start[p + 1] - rp.start[p];
-        if (w) NC(nc.Send((const u64 *)lde_cols + (u64)p * rows * w, rows * w, ncclUint64, p, nc.comm, g.stream));
-        if (wp) NC(nc.Recv((void *)rp.base[p], rows * wp, ncclUint64, p, nc.comm, g.stream));
-    }
-    NC(nc.GroupEnd());
-    if (w) CU(cudaMemcpyAsync((void *)rp.base[me], (const u64 *)lde_cols + (u64)me * rows * w, rows * w * 8, cudaMemcpyDeviceToDevice, g.stream));
-    CU(cudaEventRecord(g.ev[1], g.stream));
-
-    poseidon::launch_linear_hash_panels((u64 *)subtree, rp, rows, g.stream);
-    g.launches++;
-    CU(cudaGetLastError());
-    CU(cudaEventRecord(g.ev[2], g.stream));
+    TRY(mgpu_exchange_and_hash((const u64 *)lde_cols, (u64 *)row_panels, (u64 *)subtree, rows, w, ncols_total, nullptr));
     g.launches += poseidon::launch_tree_levels((u64 *)subtree, rows, g.stream);
     CU(cudaGetLastError());
     TRY(mgpu_top((const u64 *)subtree + gl_tree_num_elements(rows) - 4, root));
@@ -1062,31 +1104,7 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
     }
     CU(cudaEventRecord(g.ev[4], g.stream));
 
-    // all-to-all, as in gl_commit_mgpu
-    poseidon::RowPanels rp = {};
-    rp.npanels = (u32)G;
-    for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
-    for (int p = 0; p < G; p++) rp.base[p] = (const u64 *)row_panels + rows * rp.start[p];
-    NC(nc.GroupStart());
-    for (int p = 0; p < G; p++) {
-        if (p == me) continue;
-        const u64 wp = rp.start[p + 1] - rp.start[p];
-        if (w) NC(nc.Send((const u64 *)lde_cols + (u64)p * rows * w, rows * w, ncclUint64, p, nc.comm, g.stream));
-        if (wp) NC(nc.Recv((void *)rp.base[p], rows * wp, ncclUint64, p, nc.comm, g.stream));
-    }
-    NC(nc.GroupEnd());
-    if (w) CU(cudaMemcpyAsync((void *)rp.base[me], (const u64 *)lde_cols + (u64)me * rows * w, rows * w * 8, cudaMemcpyDeviceToDevice, g.stream));
-    CU(cudaEventRecord(g.ev[1], g.stream));
-
-    // the panels leave for the host while they are being hashed
-    if (row_panels_host) {
-        CU(cudaStreamWaitEvent(g.s_d2h, g.ev[1], 0));
-        CU(cudaMemcpyAsync(row_panels_host, row_panels, rows * ncols_total * 8, cudaMemcpyDeviceToHost, g.s_d2h));
-    }
-    poseidon::launch_linear_hash_panels((u64 *)subtree, rp, rows, g.stream);
-    g.launches++;
-    CU(cudaGetLastError());
-    CU(cudaEventRecord(g.ev[2], g.stream));
+    TRY(mgpu_exchange_and_hash((const u64 *)lde_cols, (u64 *)row_panels, (u64 *)subtree, rows, w, ncols_total, (u64 *)row_panels_host));
     g.launches += poseidon::launch_tree_levels((u64 *)subtree, rows, g.stream);
     CU(cudaGetLastError());
     TRY(mgpu_top((const u64 *)subtree + gl_tree_num_elements(rows) - 4, root));
