@@ -185,21 +185,44 @@ int ensure_rscale(u32 logn)
     return GL_OK;
 }
 
-template <int B2, bool LAST>
-int launch_pass_t(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
+template <int B2, bool LAST, int CW>
+int launch_pass_cw(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
 {
     constexpr int R = 16 << B2;
     size_t smem = B2 > 0 ? (size_t)R * ntt::kTileCols * 8 : 0;
     static bool attr_done = false;
     if (!attr_done && smem > 48 * 1024) {
-        CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_done = true;
     }
-    dim3 grid((unsigned)ntiles, coltiles), block(32, 1 << B2);
-    ntt::k_pass<B2, LAST><<<grid, block, smem, g.stream>>>(p);
+    dim3 grid((unsigned)(ntiles / (ntt::kTileCols / CW)), coltiles), block(32, 1 << B2);
+    ntt::k_pass<B2, LAST, CW><<<grid, block, smem, g.stream>>>(p);
     g.launches++;
     CU(cudaGetLastError());
     return GL_OK;
+}
+
+// Full 32-column tiles in one launch; a ragged remainder of <= 16 (<= 8) columns in a second launch that packs two
+// (four) row-tiles into each warp -- only for the wide passes of large transforms, where it matters.
+template <int B2, bool LAST>
+int launch_pass_t(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
+{
+    const u32 rag = p.ncols % ntt::kTileCols;
+    if (B2 >= 3 && rag != 0 && rag <= 16 && ntiles >= 4) {
+        const u32 full = p.ncols - rag;
+        if (full) {
+            ntt::PassParams q = p;
+            q.ncols = full;
+            TRY((launch_pass_cw<B2, LAST, ntt::kTileCols>(q, ntiles, coltiles - 1)));
+        }
+        ntt::PassParams q = p;
+        q.src = p.src + full;
+        q.dst = p.dst + full;
+        q.ncols = rag;
+        if (B2 >= 3 && rag <= 8) return launch_pass_cw<(B2 >= 3 ? B2 : 3), LAST, 8>(q, ntiles, 1);
+        return launch_pass_cw<(B2 >= 3 ? B2 : 3), LAST, 16>(q, ntiles, 1);
+    }
+    return launch_pass_cw<B2, LAST, ntt::kTileCols>(p, ntiles, coltiles);
 }
 
 int launch_pass(const ntt::PassParams &p)

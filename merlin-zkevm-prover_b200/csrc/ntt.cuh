@@ -140,17 +140,20 @@ template <int B2> struct Step2 {
 // coalesced segments, conflict-free shared memory, warp-uniform twiddles).
 //   LAST = false: in-place positions, output k of the tile is multiplied by w_n^(prev*low*k) (table lookup).
 //   LAST = true : natural-order (or index-reversed, for the inverse) output rows, optional scale, canonical words.
-template <int B2, bool LAST>
+//   CW < 32 (ragged last column tile): the 32 lanes of a warp are 32/CW row-tiles x CW columns, so a block of
+//   11 columns keeps 22 of 32 lanes busy instead of 11; tile index and inter-pass twiddle then differ between the
+//   lane groups (per-lane instead of warp-uniform), everything that depends only on threadIdx.y stays uniform.
+template <int B2, bool LAST, int CW = kTileCols>
 __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k_pass(const PassParams p)
 {
     constexpr int R2 = 1 << B2;
     constexpr int R = 16 * R2;
     extern __shared__ u64 tile[]; // [R][32]   (only when B2 > 0)
 
-    const u32 c = threadIdx.x, t = threadIdx.y;
-    const u32 col = blockIdx.y * kTileCols + c;
+    const u32 c = threadIdx.x, t = threadIdx.y; // c = lane: the thread's slot in a shared-memory row
+    const u32 col = blockIdx.y * CW + (c % CW);
     const bool colok = col < p.ncols;
-    const u64 tau = blockIdx.x;
+    const u64 tau = (u64)blockIdx.x * (kTileCols / CW) + c / CW;
     const u64 hi = tau >> p.log_rest, low = tau & ((1ULL << p.log_rest) - 1);
     const u64 base_in = ((hi * R) << p.log_rest) + low;
 
