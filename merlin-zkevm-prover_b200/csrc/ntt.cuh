@@ -157,11 +157,23 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     const u64 hi = tau >> p.log_rest, low = tau & ((1ULL << p.log_rest) - 1);
     const u64 base_in = ((hi * R) << p.log_rest) + low;
 
+    // rows row0 + i1 * rstep, i1 < 16; the first iv of them are below nvalid (the rest read as zeros)
     u64 x[16];
+    {
+        const u64 row0 = base_in + ((u64)t << p.log_rest);
+        const u32 rshift = p.log_rest + B2; // rstep = R2 << log_rest
+        u32 iv = 0;
+        if (colok && p.nvalid > row0) {
+            const u64 q = ((p.nvalid - row0 - 1) >> rshift) + 1;
+            iv = q < 16 ? (u32)q : 16u;
+        }
+        const u64 *sp = p.src + row0 * p.spitch + col;
+        const u64 sstep = p.spitch << rshift;
 #pragma unroll
-    for (int i1 = 0; i1 < 16; i1++) {
-        const u64 row = base_in + (((u64)i1 * R2 + t) << p.log_rest);
-        x[i1] = (colok && row < p.nvalid) ? p.src[row * p.spitch + col] : 0;
+        for (int i1 = 0; i1 < 16; i1++) {
+            x[i1] = (u32)i1 < iv ? *sp : 0;
+            sp += sstep;
+        }
     }
 
     // ---- step 1: radix-16 over i1 (row = (i1*R2 + t) within the tile)
@@ -198,22 +210,21 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     }
     const u32 tw_shift = p.log_prev + p.log_roots - p.logn;
     const u64 nmask = (1ULL << p.logn) - 1;
+    // output index k = k0 + kc(i): k0 depends on the thread row t, kc on the register index only
+    const u32 k0 = B2 > 0 ? (16 * t) / R2 : 0;
+    const u64 dstep = p.dpitch << p.log_rest;                                 // non-last: one output index further
+    u64 *dp0 = p.dst + (base_in + ((u64)k0 << p.log_rest)) * p.dpitch + col;
+    const u64 e1 = low << tw_shift;                                           // non-last: twiddle index step per output index
+    const u64 *tw0 = p.roots + e1 * k0;
 #pragma unroll
     for (int i = 0; i < 16; i++) {
-        u32 k;
-        if (B2 > 0) {
-            const int g = i / R2;
-            const int k2 = bitrev(i % R2, B2);
-            k = (16 * t) / R2 + g + 16 * k2;
-        } else {
-            k = bitrev(i, 4);
-        }
+        const u32 kc = B2 > 0 ? (u32)(i / R2 + 16 * bitrev(i % R2, B2)) : (u32)bitrev(i, 4);
         u64 v = x[i];
         if (!LAST) {
-            v = gl::mul(v, p.roots[(low * k) << tw_shift]);
-            if (colok) p.dst[(base_in + ((u64)k << p.log_rest)) * p.dpitch + col] = v;
+            v = gl::mul(v, tw0[e1 * kc]);
+            if (colok) dp0[dstep * kc] = v;
         } else {
-            u64 row = out_base + ((u64)k << p.log_prev);
+            u64 row = out_base + ((u64)(k0 + kc) << p.log_prev);
             if (p.inverse) row = (0 - row) & nmask;
             if (p.scale_mode == 1) v = gl::mul(v, p.cscale);
             else if (p.scale_mode == 2) v = gl::mul(v, p.rscale[row]);
