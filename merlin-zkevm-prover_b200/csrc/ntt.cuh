@@ -214,14 +214,13 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     const u32 k0 = B2 > 0 ? (16 * t) / R2 : 0;
     const u64 dstep = p.dpitch << p.log_rest;                                 // non-last: one output index further
     u64 *dp0 = p.dst + (base_in + ((u64)k0 << p.log_rest)) * p.dpitch + col;
-    const u64 e1 = low << tw_shift;                                           // non-last: twiddle index step per output index
-    const u64 *tw0 = p.roots + e1 * k0;
+    const u32 e1 = (u32)(low << tw_shift);                                    // non-last: twiddle index step per output index (index < 2^log_roots <= 2^27)
 #pragma unroll
     for (int i = 0; i < 16; i++) {
         const u32 kc = B2 > 0 ? (u32)(i / R2 + 16 * bitrev(i % R2, B2)) : (u32)bitrev(i, 4);
         u64 v = x[i];
         if (!LAST) {
-            v = gl::mul(v, tw0[e1 * kc]);
+            v = gl::mul(v, p.roots[e1 * (k0 + kc)]);
             if (colok) dp0[dstep * kc] = v;
         } else {
             u64 row = out_base + ((u64)(k0 + kc) << p.log_prev);
