@@ -215,13 +215,21 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     const u64 dstep = p.dpitch << p.log_rest;                                 // non-last: one output index further
     u64 *dp0 = p.dst + (base_in + ((u64)k0 << p.log_rest)) * p.dpitch + col;
     const u32 e1 = (u32)(low << tw_shift);                                    // non-last: twiddle index step per output index (index < 2^log_roots <= 2^27)
+    // walk the outputs in ascending kc so that the store pointer advances by compile-time multiples of dstep
+    u32 kprev = 0;
 #pragma unroll
-    for (int i = 0; i < 16; i++) {
-        const u32 kc = B2 > 0 ? (u32)(i / R2 + 16 * bitrev(i % R2, B2)) : (u32)bitrev(i, 4);
+    for (int j = 0; j < 16; j++) {
+        // j-th smallest kc: kc = g + 16*k2 with g = j % (16/R2), k2 = j / (16/R2); it lives in register i = g*R2 + bitrev(k2)
+        constexpr int G = 16 / R2;
+        const int g = B2 > 0 ? j % G : 0, k2 = B2 > 0 ? j / G : 0;
+        const int i = B2 > 0 ? g * R2 + bitrev(k2, B2) : bitrev(j, 4);
+        const u32 kc = B2 > 0 ? (u32)(g + 16 * k2) : (u32)j;
         u64 v = x[i];
         if (!LAST) {
             v = gl::mul(v, p.roots[e1 * (k0 + kc)]);
-            if (colok) dp0[dstep * kc] = v;
+            dp0 += dstep * (kc - kprev);
+            kprev = kc;
+            if (colok) *dp0 = v;
         } else {
             u64 row = out_base + ((u64)(k0 + kc) << p.log_prev);
             if (p.inverse) row = (0 - row) & nmask;
