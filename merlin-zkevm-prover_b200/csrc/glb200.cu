@@ -273,7 +273,7 @@ int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpit
     p.roots = g.roots;
     p.log_roots = g.log_roots;
     p.rscale = g.rscale;
-    p.cscale = scale_mode == 1 ? hpow((P + 1) / 2, logn) : 0; // 2^-logn
+    p.cscale = scale_mode == 1 ? hpow((P + 1) / 2, logn) : 1; // 2^-logn (1: unscaled)
     u32 prev = 0;
     for (u32 i = 0; i < m; i++) {
         p.pass = i;

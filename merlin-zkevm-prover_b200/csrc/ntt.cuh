@@ -106,6 +106,8 @@ __device__ __forceinline__ void dft_regs(u64 *x)
     }
 }
 
+template <int V> struct IntTag { static constexpr int value = V; };
+
 struct PassParams {
     const u64 *src;
     u64 *dst;
@@ -215,6 +217,12 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     const u64 dstep = p.dpitch << p.log_rest;                                 // non-last: one output index further
     u64 *dp0 = p.dst + (base_in + ((u64)k0 << p.log_rest)) * p.dpitch + col;
     const u32 e1 = (u32)(low << tw_shift);                                    // non-last: twiddle index step per output index (index < 2^log_roots <= 2^27)
+    // last pass: the mode is warp-uniform; each mode gets its own copy of the store loop (LMODE 0 forward, 1 inverse
+    // scaled by 1/n, 2 inverse scaled by 7^row/n) instead of re-testing it per element
+    const u64 lstep = p.dpitch << p.log_prev;
+    u64 *lp = p.dst + (out_base + ((u64)k0 << p.log_prev)) * p.dpitch + col;
+    auto store_all = [&](auto lmode_tag) {
+    constexpr int LMODE = decltype(lmode_tag)::value;
     // walk the outputs in ascending kc so that the store pointer advances by compile-time multiples of dstep
     u32 kprev = 0;
 #pragma unroll
@@ -230,14 +238,20 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
             dp0 += dstep * (kc - kprev);
             kprev = kc;
             if (colok) *dp0 = v;
+        } else if (LMODE == 0) { // forward: natural rows, one running pointer
+            lp += lstep * (kc - kprev);
+            kprev = kc;
+            if (colok) *lp = gl::canon(v);
         } else {
-            u64 row = out_base + ((u64)(k0 + kc) << p.log_prev);
-            if (p.inverse) row = (0 - row) & nmask;
-            if (p.scale_mode == 1) v = gl::mul(v, p.cscale);
-            else if (p.scale_mode == 2) v = gl::mul(v, p.rscale[row]);
+            const u64 row = (0 - (out_base + ((u64)(k0 + kc) << p.log_prev))) & nmask;
+            v = gl::mul(v, LMODE == 1 ? p.cscale : p.rscale[row]);
             if (colok) p.dst[row * p.dpitch + col] = gl::canon(v);
         }
     }
+    };
+    if (!LAST || !p.inverse) store_all(IntTag<0>());
+    else if (p.scale_mode == 2) store_all(IntTag<2>());
+    else store_all(IntTag<1>()); // cscale is 1 when the caller asked for no scaling
 }
 
 // Table builders: roots[i] = w_(2^log_roots)^i ; rscale[i] = 7^i / 2^logn.
