@@ -23,6 +23,14 @@
 #include "gl64.cuh"
 #include "poseidon_constants.cuh"
 
+// loop unrolling of the dense layer / the partial rounds (tools/ubench leaf: 1 is best or equal)
+#ifndef GLB_PARTIAL_UNROLL
+#define GLB_PARTIAL_UNROLL 1
+#endif
+#ifndef GLB_DENSE_UNROLL
+#define GLB_DENSE_UNROLL 1
+#endif
+
 namespace poseidon {
 
 using gl::u32;
@@ -169,7 +177,8 @@ __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 #pragma unroll
     for (int j = 0; j < 12; j++) o[j] = s[j];
 #endif
-#pragma unroll 1
+    constexpr int kUnroll = GLB_DENSE_UNROLL;
+#pragma unroll kUnroll
     for (int i = 0; i < 12; i++) {
 #ifdef GLB_DENSE_F64
         DotF d;
@@ -196,7 +205,8 @@ __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 // s_i += t * S_col[i].
 __device__ __forceinline__ void partial_rounds(u64 (&s)[12])
 {
-#pragma unroll 1
+    constexpr int kUnroll = GLB_PARTIAL_UNROLL;
+#pragma unroll kUnroll
     for (int r = 0; r < 22; r++) {
         const u64 t = sbox_add(s[0], c_RCP[r]);
 #ifdef GLB_PARTIAL_F64
