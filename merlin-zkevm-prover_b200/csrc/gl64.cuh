@@ -11,9 +11,9 @@
 // canonical.
 //
 // Instruction budget (cuobjdump, sm_100a): mul = 4 IMAD.WIDE + 3 IADD3 (128-bit product) +
-// ~8 for the reduction (2^64 = 2^32-1, 2^96 = -1 mod p) ~ 15 SASS instructions, split about
-// evenly between the FMA pipe (IMAD*) and the ALU pipe (IADD3*), which is what the SM can
-// dual-issue (each pipe takes one warp instruction every other cycle).
+// ~8 for the reduction (2^64 = 2^32-1, 2^96 = -1 mod p) ~ 15 SASS instructions.  On this SM the
+// integer instructions do not overlap each other (profiles/r1_02_ubench_issue_mix.txt: IMAD.WIDE,
+// LOP3, SHF, SEL cost 2 issue clocks per warp, IADD3 1-1.5), so the instruction count is the cost.
 #pragma once
 #include <stdint.h>
 

@@ -17,7 +17,8 @@
 //   DFT (twiddles are powers of w_16 = 2^12), the w_R^(t*k) twiddle, one exchange through
 //   shared memory, a radix-R/16 DFT, the per-tile geometric twiddle/scale table, store.
 //
-// Roofline: HBM, 16 B per element per pass (one read + one write).
+// Roofline: 16 B of HBM traffic per element per pass (one read + one write), but the pass is bound by integer
+// instruction issue first: 129 instructions per element per 8-bit pass (profiles/r1_17_ntt_ncu.txt).
 #pragma once
 #include "gl64.cuh"
 #include <cuda_runtime.h>

@@ -17,8 +17,9 @@
 //     every partial round) are accumulated lazily in six carry-free 64-bit columns (gl::Dot: the
 //     constant is pre-split into 22/21/21-bit limbs, 6 IMAD.WIDE per product, no ALU work) and
 //     reduced once per dot product instead of once per term.
-//   * The circulant MDS layers use the small entries (< 64) directly: 24 IMAD.WIDE per output on
-//     32-bit halves and one 96-bit reduction.
+//   * The circulant MDS layers use the small entries (< 64) directly: 24 multiply-adds per output on
+//     32-bit halves and one 96-bit reduction -- issued as exact DFMAs on the otherwise idle FP64 pipe
+//     (mds_layer below; profiles/r1_09_ubench_fp64.txt, r1_10_perm_mds_fp64_vs_int.txt).
 #pragma once
 #include "gl64.cuh"
 #include "poseidon_constants.cuh"
