@@ -163,6 +163,61 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
 #endif
 }
 
+// (M*M)[j][i] = sum_k M[j][k] M[k][i]: entries <= 6818, column sums <= 67784 < 2^17 (so a 12-term sum of 32-bit halves
+// times these entries stays below 2^49 and is exact in a double next to the 2^52 bias).
+__device__ __forceinline__ constexpr u32 mds2_entry(int j, int i)
+{
+    u32 acc = 0;
+    for (int k = 0; k < 12; k++) acc += mds_entry(j, k) * mds_entry(k, i);
+    return acc;
+}
+
+// TWO consecutive partial rounds in one layer.  On entry s = a_r (the state of round r with its S-box already applied to
+// word 0).  Round r+1 only needs word 0 of M a_r:  x = <M[.][0], a_r>,  y = x^7 + c_next,  d = y - x;  then
+//     v_{r+2} = M (M a_r + d e_0) = (M M) a_r + d M[0][.],
+// so the second matrix product collapses into the first with the squared matrix plus a rank-1 term: 12 + 1 outputs of
+// 24 (+2) DFMAs instead of 24 outputs, and one reduction per word instead of two.
+__device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
+{
+    constexpr u64 DM = neg_mod_p((unsigned __int128)(kTwo52Bits % gl::P) * (((u64)1 << 32) + 1));
+    double lo[12], hi[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++) {
+        lo[j] = u32_to_f64((u32)s[j]);
+        hi[j] = u32_to_f64((u32)(s[j] >> 32));
+    }
+    u64 x;
+    {
+        double dl = kTwo52 + (double)(DM & 0xFFFFFFFFu), dh = kTwo52 + (double)(DM >> 32);
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            dl = fma((double)mds_entry(j, 0), lo[j], dl);
+            dh = fma((double)mds_entry(j, 0), hi[j], dh);
+        }
+        const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh);
+        const u64 t = (L >> 32) + H;
+        x = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+    }
+    const u64 y = sbox_add(x, c_next);
+    const u64 d = gl::sub(y, x);
+    const double dlo = u32_to_f64((u32)d), dhi = u32_to_f64((u32)(d >> 32));
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+        double dl = kTwo52 + (double)(DM & 0xFFFFFFFFu), dh = kTwo52 + (double)(DM >> 32);
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            dl = fma((double)mds2_entry(j, i), lo[j], dl);
+            dh = fma((double)mds2_entry(j, i), hi[j], dh);
+        }
+        dl = fma((double)mds_entry(0, i), dlo, dl);
+        dh = fma((double)mds_entry(0, i), dhi, dh);
+        const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh); // raw: bias included
+        const u64 t = (L >> 32) + H; // < 2^64
+        s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+    }
+}
+
+#ifdef GLB_POSEIDON_SPARSE
 // Dense layer before the partial rounds: new[i] = sum_j P[j][i] old[j]   (poseidon_goldilocks.cpp:17)
 __device__ __forceinline__ void dense_layer(u64 (&s)[12])
 {
@@ -234,14 +289,29 @@ __device__ __forceinline__ void partial_rounds(u64 (&s)[12])
     }
 }
 
+#endif // GLB_POSEIDON_SPARSE
+
 // Full permutation.  Input: any representatives; output: lazily reduced.  OUT4: only s[0..4) of the result
 // are computed (all the sponge and the tree ever read: poseidon_goldilocks.cpp:242-249, 292-295) -- the last
 // MDS layer then costs a third; s[4..12) are left undefined.
+//
+// DENSE FORM (default).  The reference evaluates the 22 partial rounds in the "optimised" form: a dense 12x12
+// matrix P, then per round a 12-term dot product and a rank-1 update with 64-bit coefficients S
+// (poseidon_goldilocks.cpp:17-28).  Those matrices are a re-factorisation of the MDS matrix M: with
+// w_r = T_r v_r, T_r = diag(1, T^_r) acting on coordinates 1..11 only (so it commutes with the S-box on coordinate
+// 0 and with adding a constant there), S_r = T_{r+1} M T_r^-1, P = T_0 M and T_22 = I, the same state sequence is
+//     v_0 = M (u + C[48..60)),     v_{r+1} = M (sigma_0(v_r) + C[60+r] e_0),   r = 0..21,
+// i.e. every partial round is "x^7 + c on word 0, then the SAME small-entry MDS layer as a full round".  On this
+// machine that form is far cheaper: the MDS layer runs as exact DFMAs on the FP64 pipe beside the integer pipe
+// (mds_layer), whereas the sparse form costs 23 full 64-bit modular multiplications per round on the integer pipe.
+// The two forms are equal as maps on F_p^12 (tests/test_poseidon_dense_form.py checks it on the reference's constants;
+// every GPU parity test checks it against the reference itself).  -DGLB_POSEIDON_SPARSE selects the sparse form.
 template <bool OUT4 = false>
 __device__ __forceinline__ void permute(u64 (&s)[12])
 {
 #pragma unroll
     for (int i = 0; i < 12; i++) s[i] = gl::add_c(s[i], c_RC0[i]);
+#ifdef GLB_POSEIDON_SPARSE
 #pragma unroll 1
     for (int r = 0; r < 8; r++) {
 #pragma unroll
@@ -255,6 +325,39 @@ __device__ __forceinline__ void permute(u64 (&s)[12])
             mds_layer(s);
         }
     }
+#else
+    // 19 stages, one loop body: stages 0..3 and 15..18 are full rounds (S-box on all 12 words, MDS layer), stages 4..14
+    // are PAIRS of partial rounds (mds_pair); -DGLB_POSEIDON_SINGLE keeps one MDS layer per partial round
+#ifndef GLB_POSEIDON_SINGLE
+#pragma unroll 1
+    for (int st = 0; st < 19; st++) {
+        if (st < 4 || st >= 15) {
+            const int f = st < 4 ? st : st - 11;
+#pragma unroll
+            for (int i = 0; i < 12; i++) s[i] = sbox_add(s[i], c_RCF[f * 12 + i]);
+            if (OUT4 && st == 18) mds_layer<4>(s);
+            else mds_layer(s);
+        } else {
+            const int q = st - 4;
+            s[0] = sbox_add(s[0], c_RCP[2 * q]);
+            mds_pair(s, c_RCP[2 * q + 1]);
+        }
+    }
+#else
+#pragma unroll 1
+    for (int r = 0; r < 30; r++) {
+        if (r < 4 || r >= 26) {
+            const int f = r < 4 ? r : r - 22;
+#pragma unroll
+            for (int i = 0; i < 12; i++) s[i] = sbox_add(s[i], c_RCF[f * 12 + i]);
+        } else {
+            s[0] = sbox_add(s[0], c_RCP[r - 4]);
+        }
+        if (OUT4 && r == 29) mds_layer<4>(s);
+        else mds_layer(s);
+    }
+#endif
+#endif
 }
 
 } // namespace poseidon
