@@ -13,10 +13,9 @@
 //   * The first version (88 KB of straight-line SASS) stalled mostly on instruction fetch
 //     ("no_instruction" was the top stall).  All 8 full rounds now share ONE loop body and the 22
 //     partial rounds another; the whole permutation is ~30 KB of SASS.
-//   * Dot products against 64-bit constants (the dense pre-partial matrix and the 12-term row of
-//     every partial round) are accumulated lazily in six carry-free 64-bit columns (gl::Dot: the
-//     constant is pre-split into 22/21/21-bit limbs, 6 IMAD.WIDE per product, no ALU work) and
-//     reduced once per dot product instead of once per term.
+//   * The 22 partial rounds are evaluated in the DENSE form (x^7 + c on word 0, then the same small-entry MDS layer
+//     as a full round), two rounds per layer through the squared matrix (mds_pair) -- not in the reference's sparse
+//     form, whose 64-bit coefficients cost 23 full modular multiplications per round on the integer pipe; see permute().
 //   * The circulant MDS layers use the small entries (< 64) directly: 24 multiply-adds per output on
 //     32-bit halves and one 96-bit reduction -- issued as exact DFMAs on the otherwise idle FP64 pipe
 //     (mds_layer below; profiles/r1_09_ubench_fp64.txt, r1_10_perm_mds_fp64_vs_int.txt).
@@ -41,11 +40,13 @@ using gl::u64;
 __constant__ u64 c_RC0[12];          // pre-round constants C[0..12)
 __constant__ u64 c_RCF[8 * 12];      // constants added after the S-box of full round r (row 7 = 0)
 __constant__ u64 c_RCP[22];          // partial-round constants C[60..82)
+#ifdef GLB_POSEIDON_SPARSE // tables of the reference's sparse form (dense matrix P, sparse matrices S); see permute()
 __constant__ uint4 c_PL[12 * 12];    // dense layer: limbs of P[j][i] at [i*12 + j] (x,y,z; w unused)
 __constant__ uint4 c_SL[22 * 12];    // partial round r: limbs of the dot row S[23r + i] at [r*12 + i]
 __constant__ u64 c_SV[22 * 11];      // partial round r: rank-1 column S[23r + 12 + i], i < 11
 __constant__ double4 c_PLd[12 * 12]; // the same dense-layer / dot-row constants as four 16-bit limbs held as doubles
 __constant__ double4 c_SLd[22 * 12];
+#endif
 
 // MDS circulant (reference M[j][i] = circ[(i-j) mod 12] + 8*[i==j==0]) as immediates.
 __device__ __forceinline__ constexpr u32 mds_entry(int j, int i)

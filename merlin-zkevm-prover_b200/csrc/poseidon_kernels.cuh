@@ -195,17 +195,23 @@ __global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_tree_level(u64
 // Derive the device tables from the generated parameter header (poseidon_constants.cuh).
 inline cudaError_t upload_constants()
 {
-    static u64 rc0[12], rcf[96], rcp[22], sv[22 * 11];
-    static uint4 pl[144], sl[22 * 12];
-    static double4 pld[144], sld[22 * 12];
-    auto limbs_f64 = [](u64 c) { return make_double4((double)(c & 0xFFFF), (double)((c >> 16) & 0xFFFF), (double)((c >> 32) & 0xFFFF), (double)(c >> 48)); };
-    auto limbs = [](u64 c) { return make_uint4((u32)(c & 0x3FFFFF), (u32)((c >> 22) & 0x1FFFFF), (u32)(c >> 43), 0u); };
+    static u64 rc0[12], rcf[96], rcp[22];
     for (int i = 0; i < 12; i++) rc0[i] = GLP_RC[i];
     for (int r = 0; r < 8; r++)
         for (int i = 0; i < 12; i++)
             rcf[r * 12 + i] = r < 4 ? GLP_RC[(r + 1) * 12 + i] : (r < 7 ? GLP_RC[82 + 12 * (r - 4) + i] : 0);
+    for (int r = 0; r < 22; r++) rcp[r] = GLP_RC[60 + r];
+    cudaError_t e;
+    if ((e = cudaMemcpyToSymbol(c_RC0, rc0, sizeof rc0)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_RCF, rcf, sizeof rcf)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyToSymbol(c_RCP, rcp, sizeof rcp)) != cudaSuccess) return e;
+#ifdef GLB_POSEIDON_SPARSE
+    static u64 sv[22 * 11];
+    static uint4 pl[144], sl[22 * 12];
+    static double4 pld[144], sld[22 * 12];
+    auto limbs = [](u64 c) { return make_uint4((u32)(c & 0x3FFFFF), (u32)((c >> 22) & 0x1FFFFF), (u32)(c >> 43), 0u); };
+    auto limbs_f64 = [](u64 c) { return make_double4((double)(c & 0xFFFF), (double)((c >> 16) & 0xFFFF), (double)((c >> 32) & 0xFFFF), (double)(c >> 48)); };
     for (int r = 0; r < 22; r++) {
-        rcp[r] = GLP_RC[60 + r];
         if (GLP_SP[23 * r] != 25) return cudaErrorInvalidValue; // partial_rounds() hard-codes this coefficient
         for (int i = 0; i < 12; i++) sl[r * 12 + i] = limbs(GLP_SP[23 * r + i]);
         for (int i = 0; i < 12; i++) sld[r * 12 + i] = limbs_f64(GLP_SP[23 * r + i]);
@@ -216,15 +222,12 @@ inline cudaError_t upload_constants()
             pl[i * 12 + j] = limbs(GLP_PM[j * 12 + i]);
             pld[i * 12 + j] = limbs_f64(GLP_PM[j * 12 + i]);
         }
-    cudaError_t e;
-    if ((e = cudaMemcpyToSymbol(c_RC0, rc0, sizeof rc0)) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_RCF, rcf, sizeof rcf)) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_RCP, rcp, sizeof rcp)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_PL, pl, sizeof pl)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_SL, sl, sizeof sl)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_SV, sv, sizeof sv)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_PLd, pld, sizeof pld)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_SLd, sld, sizeof sld)) != cudaSuccess) return e;
+#endif
     return cudaSuccess;
 }
 
