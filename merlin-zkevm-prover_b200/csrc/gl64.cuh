@@ -33,47 +33,11 @@ struct u128 {
 // carry-out predicate; with an immediate it strength-reduces to IMAD.IADD + IMAD.HI (half rate).
 __constant__ u32 c_eps[2] = {0xFFFFFFFFu, 0u};
 
-// acc += a * b (32x32 -> 64, no overflow expected by the caller).  Written as a carry chain: ptxas
-// fuses the pair into one IMAD.WIDE.U32 with the accumulator as addend and, unlike mad.wide.u32,
-// does not re-associate a chain of them into multiplies + 3-input adds.
-__device__ __forceinline__ void madw(u64 &acc, u32 a, u32 b)
-{
-    u32 lo = (u32)acc, hi = (u32)(acc >> 32);
-    asm("mad.lo.cc.u32 %0, %2, %3, %0;\n\tmadc.hi.u32 %1, %2, %3, %1;" : "+r"(lo), "+r"(hi) : "r"(a), "r"(b));
-    acc = ((u64)hi << 32) | lo;
-}
-
 __device__ __forceinline__ u64 pack(u32 lo, u32 hi) { return ((u64)hi << 32) | lo; }
 
 // x mod p for x < 2^64: x >= p  <=>  x + (2^32-1) carries out of 64 bits, and then x - p = x + (2^32-1) - 2^64.
 // Written so that ptxas emits IADD3, IADD3.X, SEL, IMAD.WIDE (4 instructions; the compare form needs 6).
 __device__ __forceinline__ u64 canon_slow(u64 x) { return x >= P ? x - P : x; }
-
-// 64x64 -> 128, even/odd column scheme: 4 wide multiplies, one carry chain.
-__device__ __forceinline__ u128 mul_wide(u64 a, u64 b)
-{
-    u32 a0 = (u32)a, a1 = (u32)(a >> 32), b0 = (u32)b, b1 = (u32)(b >> 32);
-    u128 r;
-    asm("{\n\t"
-        ".reg .u64 p, q, y;\n\t"
-        ".reg .u32 p1, q0, q1, y0, y1, c;\n\t"
-        "mul.wide.u32 p, %4, %6;\n\t"
-        "mul.wide.u32 q, %5, %7;\n\t"
-        "mul.wide.u32 y, %4, %7;\n\t"
-        "mov.b64 {%0, p1}, p;\n\t"
-        "mov.b64 {q0, q1}, q;\n\t"
-        "mov.b64 {y0, y1}, y;\n\t"
-        "mad.lo.cc.u32 y0, %5, %6, y0;\n\t"
-        "madc.hi.cc.u32 y1, %5, %6, y1;\n\t"
-        "addc.u32 c, 0, 0;\n\t"
-        "add.cc.u32 %1, p1, y0;\n\t"
-        "addc.cc.u32 %2, q0, y1;\n\t"
-        "addc.u32 %3, q1, c;\n\t"
-        "}"
-        : "=r"(r.x0), "=r"(r.x1), "=r"(r.x2), "=r"(r.x3)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
-    return r;
-}
 
 // a*b + c as a 128-bit value (cannot overflow: (2^64-1)^2 + 2^64-1 < 2^128).
 __device__ __forceinline__ u128 mad_wide(u64 a, u64 b, u64 c)
@@ -165,32 +129,6 @@ __device__ __forceinline__ u64 reduce160(u32 x0, u32 x1, u32 x2, u32 x3, u32 x4)
         : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(x4), "r"(c_eps[0]));
     return pack(r0, r1);
 }
-
-// Lazy dot-product accumulator: sum of up to 32 products a*c with a any u64 and c a constant < 2^64
-// given as limbs c = l0 + l1 2^22 + l2 2^43 (22/21/21 bits).  Six 64-bit column sums (a half x limb
-// < 2^54), no carries while accumulating; one fold() per dot product.
-struct Dot {
-    u64 c00, c01, c02, c10, c11, c12;
-    __device__ __forceinline__ void zero() { c00 = c01 = c02 = c10 = c11 = c12 = 0; }
-    __device__ __forceinline__ void mad(u64 a, u32 l0, u32 l1, u32 l2)
-    {
-        u32 a0 = (u32)a, a1 = (u32)(a >> 32);
-        madw(c00, a0, l0); madw(c01, a0, l1); madw(c02, a0, l2);
-        madw(c10, a1, l0); madw(c11, a1, l1); madw(c12, a1, l2);
-    }
-    __device__ __forceinline__ u64 fold() const
-    {
-        typedef unsigned __int128 w128;
-        w128 i0 = (w128)c00 + ((w128)c01 << 22) + ((w128)c02 << 43);
-        w128 i1 = (w128)c10 + ((w128)c11 << 22) + ((w128)c12 << 43);
-        u64 lo = (u64)i0, hi = (u64)(i0 >> 64), l1 = (u64)i1, h1 = (u64)(i1 >> 64);
-        u32 x0 = (u32)lo, x1 = (u32)(lo >> 32), x2 = (u32)hi, x3 = (u32)(hi >> 32), x4;
-        asm("add.cc.u32 %0, %0, %4;\n\taddc.cc.u32 %1, %1, %5;\n\taddc.cc.u32 %2, %2, %6;\n\taddc.u32 %3, %7, 0;"
-            : "+r"(x1), "+r"(x2), "+r"(x3), "=r"(x4)
-            : "r"((u32)l1), "r"((u32)(l1 >> 32)), "r"((u32)h1), "r"((u32)(h1 >> 32)));
-        return reduce160(x0, x1, x2, x3, x4);
-    }
-};
 
 // nvcc's native 128-bit product is one instruction shorter than mul_wide (the cross-term carry rides
 // on IMAD.WIDE.U32.X instead of a SEL): 4 IMAD.WIDE + 3 ALU, then the 8-instruction reduction.

@@ -205,29 +205,6 @@ inline cudaError_t upload_constants()
     if ((e = cudaMemcpyToSymbol(c_RC0, rc0, sizeof rc0)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_RCF, rcf, sizeof rcf)) != cudaSuccess) return e;
     if ((e = cudaMemcpyToSymbol(c_RCP, rcp, sizeof rcp)) != cudaSuccess) return e;
-#ifdef GLB_POSEIDON_SPARSE
-    static u64 sv[22 * 11];
-    static uint4 pl[144], sl[22 * 12];
-    static double4 pld[144], sld[22 * 12];
-    auto limbs = [](u64 c) { return make_uint4((u32)(c & 0x3FFFFF), (u32)((c >> 22) & 0x1FFFFF), (u32)(c >> 43), 0u); };
-    auto limbs_f64 = [](u64 c) { return make_double4((double)(c & 0xFFFF), (double)((c >> 16) & 0xFFFF), (double)((c >> 32) & 0xFFFF), (double)(c >> 48)); };
-    for (int r = 0; r < 22; r++) {
-        if (GLP_SP[23 * r] != 25) return cudaErrorInvalidValue; // partial_rounds() hard-codes this coefficient
-        for (int i = 0; i < 12; i++) sl[r * 12 + i] = limbs(GLP_SP[23 * r + i]);
-        for (int i = 0; i < 12; i++) sld[r * 12 + i] = limbs_f64(GLP_SP[23 * r + i]);
-        for (int i = 0; i < 11; i++) sv[r * 11 + i] = GLP_SP[23 * r + 12 + i];
-    }
-    for (int i = 0; i < 12; i++)
-        for (int j = 0; j < 12; j++) {
-            pl[i * 12 + j] = limbs(GLP_PM[j * 12 + i]);
-            pld[i * 12 + j] = limbs_f64(GLP_PM[j * 12 + i]);
-        }
-    if ((e = cudaMemcpyToSymbol(c_PL, pl, sizeof pl)) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_SL, sl, sizeof sl)) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_SV, sv, sizeof sv)) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_PLd, pld, sizeof pld)) != cudaSuccess) return e;
-    if ((e = cudaMemcpyToSymbol(c_SLd, sld, sizeof sld)) != cudaSuccess) return e;
-#endif
     return cudaSuccess;
 }
 
