@@ -121,6 +121,23 @@ int need_ctx()
     return GL_OK;
 }
 
+// The library owns ONE stream, ONE scratch arena and one set of timing events, so the public calls are serialised:
+// the reference's callers are single-threaded per prover (prover.cpp:187-258) except FRIProve::prove, which builds
+// NTT_Goldilocks(nX, 1) and calls INTT from inside an OpenMP region (friProve.cpp:44-107).  Recursive because the
+// *_host entry points are written on top of the *_dev ones.  The CUDA "current device" is per host thread, so every
+// entry also binds the calling thread to the library's device.
+std::recursive_mutex g_api_mu;
+int enter_api()
+{
+    TRY(need_ctx());
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || cur != g.device) CU(cudaSetDevice(g.device));
+    return GL_OK;
+}
+#define API_ENTER()                                         \
+    std::lock_guard<std::recursive_mutex> api_lock_(g_api_mu); \
+    TRY(enter_api())
+
 int arena_reserve(size_t bytes)
 {
     if (bytes <= g.arena_bytes) return GL_OK;
@@ -636,6 +653,7 @@ int gl_init(int device)
 
 void gl_shutdown(void)
 {
+    std::lock_guard<std::recursive_mutex> api_lock_(g_api_mu);
     std::lock_guard<std::mutex> lk(g.mu);
     if (!g.ready) return;
     cudaStreamSynchronize(g.stream);
@@ -672,7 +690,7 @@ uint64_t gl_kernel_launches(int reset)
 
 int gl_dev_alloc(void **dptr, size_t bytes)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaMalloc(dptr, bytes ? bytes : 8));
     return GL_OK;
 }
@@ -683,7 +701,7 @@ int gl_dev_free(void *dptr)
 }
 int gl_host_alloc(void **hptr, size_t bytes)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaHostAlloc(hptr, bytes ? bytes : 8, cudaHostAllocDefault));
     return GL_OK;
 }
@@ -694,21 +712,21 @@ int gl_host_free(void *hptr)
 }
 int gl_h2d(void *dptr, const void *hptr, size_t bytes)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaMemcpyAsync(dptr, hptr, bytes, cudaMemcpyHostToDevice, g.stream));
     CU(cudaStreamSynchronize(g.stream));
     return GL_OK;
 }
 int gl_d2h(void *hptr, const void *dptr, size_t bytes)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaMemcpyAsync(hptr, dptr, bytes, cudaMemcpyDeviceToHost, g.stream));
     CU(cudaStreamSynchronize(g.stream));
     return GL_OK;
 }
 int gl_sync(void)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaStreamSynchronize(g.stream));
     return GL_OK;
 }
@@ -731,7 +749,7 @@ int gl_last_timings(float ms[3])
 // ---- device-resident ----------------------------------------------------------------------------
 int gl_ntt_dev(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaEventRecord(g.ev[0], g.stream));
     TRY(ntt_dev((u64 *)dst, (const u64 *)src, size, ncols, inverse, extend));
     CU(cudaEventRecord(g.ev[1], g.stream));
@@ -740,7 +758,7 @@ int gl_ntt_dev(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols
 
 int gl_extend_pol_dev(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaEventRecord(g.ev[0], g.stream));
     TRY(extend_pol_dev((u64 *)out, (const u64 *)in, n_ext, n, ncols));
     CU(cudaEventRecord(g.ev[1], g.stream));
@@ -749,7 +767,7 @@ int gl_extend_pol_dev(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_
 
 int gl_merkletree_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (nrows == 0) return GL_OK;
     TRY(merkletree_dev((u64 *)tree, (const u64 *)src, ncols, nrows, true));
     return collect_timings(false, true);
@@ -758,7 +776,7 @@ int gl_merkletree_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint6
 int gl_commit_dev(uint64_t *lde, uint64_t *tree, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols,
                   uint64_t root[4])
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (n == 0 || n_ext == 0) return fail(GL_ERR_ARG, "commit: empty domain");
     CU(cudaEventRecord(g.ev[0], g.stream));
     TRY(extend_pol_dev((u64 *)lde, (const u64 *)in, n_ext, n, ncols));
@@ -771,7 +789,7 @@ int gl_commit_dev(uint64_t *lde, uint64_t *tree, const uint64_t *in, uint64_t n_
 int gl_group_proof_dev(uint64_t *proof_host, const uint64_t *src, const uint64_t *tree, uint64_t height,
                        uint64_t width, uint64_t idx)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (height == 0 || idx >= height) return fail(GL_ERR_ARG, "getGroupProof: idx %llu out of range", (u64)idx);
     u64 levels = 0;
     while ((height >> levels) > 1) levels++;
@@ -790,7 +808,7 @@ int gl_group_proof_dev(uint64_t *proof_host, const uint64_t *src, const uint64_t
 
 int gl_hash_full_result_dev(uint64_t *out, const uint64_t *in, uint64_t n)
 {
-    TRY(need_ctx());
+    API_ENTER();
     poseidon::launch_hash_full_result((u64 *)out, (const u64 *)in, n, g.stream);
     if (n) g.launches++;
     CU(cudaGetLastError());
@@ -800,7 +818,7 @@ int gl_hash_full_result_dev(uint64_t *out, const uint64_t *in, uint64_t n)
 
 int gl_linear_hash_rows_dev(uint64_t *out, const uint64_t *src, uint64_t ncols, uint64_t nrows)
 {
-    TRY(need_ctx());
+    API_ENTER();
     poseidon::launch_linear_hash_rows((u64 *)out, (const u64 *)src, nrows, ncols, g.stream);
     if (nrows) g.launches++;
     CU(cudaGetLastError());
@@ -812,7 +830,7 @@ int gl_linear_hash_rows_dev(uint64_t *out, const uint64_t *src, uint64_t ncols, 
 int gl_ntt_host(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend)
 {
     if (size == 0 || ncols == 0) return GL_OK;
-    TRY(need_ctx());
+    API_ENTER();
     if (!dst) dst = (uint64_t *)src;
     size_t bytes = (size_t)size * ncols * 8;
     DevBuf d;
@@ -825,14 +843,14 @@ int gl_ntt_host(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncol
 int gl_extend_pol_host(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols)
 {
     if (n == 0 || ncols == 0) return GL_OK;
-    TRY(need_ctx());
+    API_ENTER();
     return commit_host_pipelined(out, nullptr, in, n_ext, n, ncols, nullptr, false);
 }
 
 int gl_merkletree_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows)
 {
     if (nrows == 0) return GL_OK;
-    TRY(need_ctx());
+    API_ENTER();
     DevBuf s, t;
     TRY(s.alloc((size_t)nrows * ncols * 8));
     TRY(t.alloc(gl_tree_num_elements(nrows) * 8));
@@ -844,14 +862,14 @@ int gl_merkletree_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint
 int gl_commit_host(uint64_t *lde_out, uint64_t *tree_out, const uint64_t *in, uint64_t n_ext, uint64_t n,
                    uint64_t ncols, uint64_t root[4])
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (n == 0 || n_ext == 0) return fail(GL_ERR_ARG, "commit: empty domain");
     return commit_host_pipelined(lde_out, tree_out, in, n_ext, n, ncols, root, true);
 }
 
 int gl_host_register(void *hptr, size_t bytes)
 {
-    TRY(need_ctx());
+    API_ENTER();
     CU(cudaHostRegister(hptr, bytes, cudaHostRegisterDefault));
     return GL_OK;
 }
@@ -863,7 +881,7 @@ int gl_host_unregister(void *hptr)
 
 int gl_merkletree_batch_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows, uint64_t batch)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (nrows == 0) return GL_OK;
     if (batch == 0) return fail(GL_ERR_ARG, "merkletree_batch: batch size 0");
     const u64 nb = ncols > 0 ? (ncols + batch - 1) / batch : 1; // poseidon_goldilocks.cpp:122-127
@@ -883,7 +901,7 @@ int gl_merkletree_batch_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols,
 int gl_merkletree_batch_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows, uint64_t batch)
 {
     if (nrows == 0) return GL_OK;
-    TRY(need_ctx());
+    API_ENTER();
     DevBuf s, t;
     TRY(s.alloc((size_t)nrows * ncols * 8));
     TRY(t.alloc(gl_tree_num_elements(nrows) * 8));
@@ -895,7 +913,7 @@ int gl_merkletree_batch_host(uint64_t *tree, const uint64_t *src, uint64_t ncols
 int gl_hash_full_result_host(uint64_t *out, const uint64_t *in, uint64_t n)
 {
     if (n == 0) return GL_OK;
-    TRY(need_ctx());
+    API_ENTER();
     DevBuf d;
     TRY(d.alloc((size_t)n * 96));
     TRY(gl_h2d(d.p, in, (size_t)n * 96));
@@ -905,7 +923,7 @@ int gl_hash_full_result_host(uint64_t *out, const uint64_t *in, uint64_t n)
 
 int gl_linear_hash_host(uint64_t out[4], const uint64_t *in, uint64_t size)
 {
-    TRY(need_ctx());
+    API_ENTER();
     DevBuf s, o;
     TRY(s.alloc((size_t)size * 8));
     TRY(o.alloc(32));
@@ -917,7 +935,7 @@ int gl_linear_hash_host(uint64_t out[4], const uint64_t *in, uint64_t size)
 int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const uint64_t *c, uint64_t n, int op)
 {
     if (n == 0) return GL_OK;
-    TRY(need_ctx());
+    API_ENTER();
     if (op < 0 || op > 6) return fail(GL_ERR_ARG, "unknown field op %d", op);
     DevBuf d;
     TRY(d.alloc((size_t)n * 8 * 4));
@@ -933,7 +951,7 @@ int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const 
 
 int gl_fill_synthetic_dev(uint64_t *dst, uint64_t words, uint64_t seed, uint64_t first_index)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (words == 0) return GL_OK;
     k_fill_synthetic<<<148 * 8, 256, 0, g.stream>>>((u64 *)dst, words, seed, first_index);
     g.launches++;
@@ -1010,7 +1028,7 @@ int gl_mgpu_unique_id(uint8_t id[128])
 
 int gl_mgpu_init(const uint8_t id[128], int rank, int world)
 {
-    TRY(need_ctx());
+    API_ENTER();
     TRY(nccl_load());
     if (nc.comm) return fail(GL_ERR_ARG, "multi-GPU communicator already initialised");
     if (world < 1 || world > poseidon::kMaxPanels || (world & (world - 1)) || rank < 0 || rank >= world)
@@ -1026,6 +1044,7 @@ int gl_mgpu_init(const uint8_t id[128], int rank, int world)
 
 int gl_mgpu_shutdown(void)
 {
+    std::lock_guard<std::recursive_mutex> api_lock_(g_api_mu);
     if (nc.comm) {
         cudaStreamSynchronize(g.stream);
         nc.CommDestroy(nc.comm);
@@ -1043,7 +1062,7 @@ uint64_t gl_mgpu_col_start(uint64_t ncols, int world, int rank) { return col_sta
 int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, const uint64_t *in_cols, uint64_t n_ext,
                    uint64_t n, uint64_t ncols_total, uint64_t root[4])
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (!nc.comm) return fail(GL_ERR_ARG, "gl_commit_mgpu: call gl_mgpu_init first");
     const int G = nc.world, me = nc.rank;
     if (n == 0 || n_ext == 0 || !is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "commit: bad domain %llu -> %llu", (u64)n, (u64)n_ext);
@@ -1075,7 +1094,7 @@ int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, 
 int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const uint64_t *in_cols_host, uint64_t *lde_cols,
                         uint64_t *row_panels, uint64_t *subtree, uint64_t n_ext, uint64_t n, uint64_t ncols_total, uint64_t root[4])
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (!nc.comm) return fail(GL_ERR_ARG, "gl_commit_mgpu_host: call gl_mgpu_init first");
     const int G = nc.world, me = nc.rank;
     if (n == 0 || n_ext == 0 || !is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "commit: bad domain %llu -> %llu", (u64)n, (u64)n_ext);
@@ -1145,7 +1164,7 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
 
 int gl_mgpu_gather_tree(uint64_t *tree_full, const uint64_t *subtree, uint64_t n_ext)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (!nc.comm) return fail(GL_ERR_ARG, "gl_mgpu_gather_tree: call gl_mgpu_init first");
     const u64 G = (u64)nc.world, rows = n_ext / G;
     u32 lv = 0;
@@ -1170,7 +1189,7 @@ int gl_mgpu_gather_tree(uint64_t *tree_full, const uint64_t *subtree, uint64_t n
 
 int gl_fill_synthetic_cols_dev(uint64_t *dst, uint64_t nrows, uint64_t col0, uint64_t ncols_local, uint64_t ncols_total, uint64_t seed)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (nrows == 0 || ncols_local == 0) return GL_OK;
     k_fill_synthetic_cols<<<148 * 8, 256, 0, g.stream>>>((u64 *)dst, nrows, col0, ncols_local, ncols_total, seed);
     g.launches++;
@@ -1182,7 +1201,7 @@ int gl_fill_synthetic_cols_dev(uint64_t *dst, uint64_t nrows, uint64_t col0, uin
 // ---- next rows: Q-polynomial commit, FRI layer commit -----------------------------------
 int gl_q_extend_dev(uint64_t *cm4, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim, uint64_t qdeg)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (n == 0 || qdim == 0 || qdeg == 0) return GL_OK;
     if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "q_extend: bad sizes %llu -> %llu", (u64)n, (u64)n_ext);
     if (qdeg > (u64)fri::kMaxQDeg || qdeg * n > n_ext) return fail(GL_ERR_ARG, "q_extend: qDeg %llu out of range", (u64)qdeg);
@@ -1214,6 +1233,7 @@ int gl_q_extend_dev(uint64_t *cm4, const uint64_t *q_2ns, uint64_t n, uint64_t n
 int gl_q_commit_dev(uint64_t *cm4, uint64_t *tree, const uint64_t *q_2ns, uint64_t n, uint64_t n_ext, uint64_t qdim, uint64_t qdeg,
                     uint64_t root[4])
 {
+    API_ENTER();
     TRY(gl_q_extend_dev(cm4, q_2ns, n, n_ext, qdim, qdeg));
     const float lde_ms = g.ms[0];
     TRY(merkletree_dev((u64 *)tree, (const u64 *)cm4, qdim * qdeg, n_ext, true));          // starks.cpp:289
@@ -1225,7 +1245,7 @@ int gl_q_commit_dev(uint64_t *cm4, uint64_t *tree, const uint64_t *q_2ns, uint64
 
 int gl_fri_fold_dev(uint64_t *out, const uint64_t *pol, uint32_t pol_bits, uint32_t next_bits, uint64_t shift_inv, const uint64_t x[3])
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (next_bits > pol_bits || pol_bits > 32 || pol_bits - next_bits > 6) return fail(GL_ERR_ARG, "fri_fold: bits %u -> %u unsupported", pol_bits, next_bits);
     TRY(ensure_roots(pol_bits));
     fri::F3 xx = {x[0], x[1], x[2]};
@@ -1240,7 +1260,7 @@ int gl_fri_fold_dev(uint64_t *out, const uint64_t *pol, uint32_t pol_bits, uint3
 
 int gl_fri_transpose_dev(uint64_t *aux, const uint64_t *pol, uint64_t degree, uint32_t transpose_bits)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (degree == 0) return GL_OK;
     if ((degree >> transpose_bits) == 0) return fail(GL_ERR_ARG, "fri_transpose: 2^%u columns exceed the degree", transpose_bits);
     fri::k_fri_transpose<<<148 * 8, 256, 0, g.stream>>>((u64 *)aux, (const u64 *)pol, degree, transpose_bits);
@@ -1252,6 +1272,7 @@ int gl_fri_transpose_dev(uint64_t *aux, const uint64_t *pol, uint64_t degree, ui
 int gl_fri_layer_commit_dev(uint64_t *tree, uint64_t *aux, uint64_t *pol2, const uint64_t *pol, uint32_t pol_bits, uint32_t next_bits,
                             uint32_t tree_bits, uint64_t shift_inv, const uint64_t x[3], uint64_t root[4])
 {
+    API_ENTER();
     if (tree_bits > next_bits) return fail(GL_ERR_ARG, "fri_layer: tree of 2^%u groups from 2^%u elements", tree_bits, next_bits);
     TRY(gl_fri_fold_dev(pol2, pol, pol_bits, next_bits, shift_inv, x));                    // friProve.cpp:36-107
     const u64 pol2n = 1ULL << next_bits, ngroups = 1ULL << tree_bits, group = pol2n / ngroups;
@@ -1266,7 +1287,7 @@ uint64_t gl_consttree_num_elements(uint64_t npols, uint64_t n_ext) { return 2 + 
 
 int gl_build_consttree_host(uint64_t *const_tree, const uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols)
 {
-    TRY(need_ctx());
+    API_ENTER();
     if (n == 0 || n_ext == 0 || npols == 0) return fail(GL_ERR_ARG, "buildConstTree: empty input");
     const_tree[0] = npols; // header read back by MerkleTreeGL(Goldilocks::Element *tree), merkleTreeGL.hpp:24-32
     const_tree[1] = n_ext;

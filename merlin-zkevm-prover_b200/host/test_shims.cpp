@@ -5,6 +5,7 @@
 #include "merkleTreeGL.hpp"
 #include "ntt_goldilocks.hpp"
 #include <cstdio>
+#include <thread>
 #include <vector>
 
 static const uint64_t P = 0xFFFFFFFF00000001ULL;
@@ -94,6 +95,45 @@ static void test_extendPol_and_stage_commit()
     for (int k = 0; k < 4; k++) EXPECT_EQ(Goldilocks::toU64(r1[k]), Goldilocks::toU64(r2[k]));
 }
 
+// FRIProve::prove builds NTT_Goldilocks(nX, 1) and calls INTT on (nX x 3) groups from inside an OpenMP parallel region
+// (friProve.cpp:44-107): the drop-in must give every thread its own correct answer.  Each thread transforms a
+// different matrix forth and back; a forward transform of a constant column must be (n*c, 0, 0, ...).
+static void test_concurrent_callers()
+{
+    const int nthreads = 8, reps = 6;
+    const uint64_t nX = 1 << 5, ncols = 3;
+    std::vector<int> bad(nthreads, 0);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthreads; t++)
+        pool.emplace_back([&, t]() {
+            try
+            {
+                for (int rep = 0; rep < reps; rep++)
+                {
+                    NTT_Goldilocks ntt(nX, 1);
+                    std::vector<Goldilocks::Element> a(nX * ncols), init;
+                    for (uint64_t i = 0; i < nX * ncols; i++) a[i] = Goldilocks::fromU64((0x9E3779B97F4A7C15ULL * (i + 1 + 1000 * t + 77 * rep)) % P);
+                    init = a;
+                    ntt.INTT(a.data(), a.data(), nX, ncols);
+                    ntt.NTT(a.data(), a.data(), nX, ncols);
+                    for (uint64_t i = 0; i < nX * ncols; i++)
+                        if (Goldilocks::toU64(a[i]) != Goldilocks::toU64(init[i])) bad[t]++;
+                    std::vector<Goldilocks::Element> c(nX * ncols, Goldilocks::fromU64(t + 1));
+                    ntt.NTT(c.data(), c.data(), nX, ncols);
+                    for (uint64_t i = 0; i < nX * ncols; i++)
+                        if (Goldilocks::toU64(c[i]) != (i < ncols ? nX * (t + 1) : 0)) bad[t]++;
+                }
+            }
+            catch (const std::exception &e)
+            {
+                printf("FAIL thread %d: %s\n", t, e.what());
+                bad[t]++;
+            }
+        });
+    for (auto &th : pool) th.join();
+    for (int t = 0; t < nthreads; t++) EXPECT_EQ((uint64_t)bad[t], 0);
+}
+
 int main()
 {
     try
@@ -101,6 +141,7 @@ int main()
         test_merkletree();
         test_ntt_roundtrip();
         test_extendPol_and_stage_commit();
+        test_concurrent_callers();
     }
     catch (const std::exception &e)
     {

@@ -139,6 +139,43 @@ def test_ntt_errors(glb):
         glb.ntt_host(np.ones((12, 2), dtype=np.uint64))  # not a power of two (reference: assert, ntt_goldilocks.cpp:28)
 
 
+
+def test_concurrent_host_callers(glb, oracle):
+    """The reference calls the tiny INTTs of the FRI fold from inside an OpenMP region (friProve.cpp:44-107) and
+    ctypes releases the GIL, so these threads really overlap inside the C ABI: every call must still return its own
+    answer (one stream and one scratch arena are shared; the public entry points serialise)."""
+    import threading
+    rng = np.random.default_rng(77)
+    jobs = []
+    for t in range(8):
+        n = 1 << int(rng.integers(1, 11))
+        c = int(rng.integers(1, 40))
+        a = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+        jobs.append((a, bool(t & 1)))
+    want = [oracle.ntt(a, inverse=inv) for a, inv in jobs]
+    tree_src = rng.integers(0, P, size=(256, 20), dtype=np.uint64)
+    want_tree = oracle.merkletree(tree_src)
+    errors = []
+
+    def worker(k):
+        try:
+            a, inv = jobs[k]
+            for _ in range(10):
+                if not np.array_equal(glb.ntt_host(a, inverse=inv), want[k]):
+                    errors.append(("ntt", k))
+                if k == 0 and not np.array_equal(glb.merkletree_host(tree_src), want_tree):
+                    errors.append(("tree", k))
+        except Exception as ex:  # noqa: BLE001 - reported below
+            errors.append((k, repr(ex)))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(len(jobs))]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors[:4]
+
+
 def test_ntt_dev_aliasing(glb, oracle):
     """dst == src (in place) and dst != src (source preserved), as ntt_goldilocks.cpp:166-232."""
     rng = np.random.default_rng(5)
