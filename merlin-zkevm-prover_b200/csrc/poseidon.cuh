@@ -53,20 +53,12 @@ __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
 // the low and of the high 32-bit halves each fit 64 bits (< 2^42); one 96-bit reduction per output.
 //
 // The 24 multiply-adds per output run on the FP64 pipe, which issues beside the integer pipe on this SM
-// (profiles/r1_09_ubench_fp64.txt: DFMA + IMAD.WIDE pairs issue in the time of one): a 32-bit half h is the
-// double (2^52 + h) - 2^52 (register pairing + one DADD), every partial sum 2^52 + sum m*h is an integer
+// (profiles/r1_09_ubench_fp64.txt: DFMA + IMAD.WIDE pairs issue in the time of one): a 32-bit half h becomes a
+// double with ONE I2F.F64.U32 (exact; it issues on the conversion pipe, which is otherwise idle -- the earlier
+// (2^52 + h) - 2^52 form cost a DADD on the FP64 pipe plus ~2.3 register moves per half to build the pair:
+// 1359 -> 1398 M perm/s, profiles/r1_21_leaf_variants.txt), every partial sum 2^52 + sum m*h is an integer
 // below 2^53 and therefore exact, and the low 52 bits of the final double ARE the integer sum.
-__device__ __forceinline__ double u32_to_f64_pair(u32 h) { return __hiloint2double(0x43300000, (int)h) - 4503599627370496.0; }
-__device__ __forceinline__ double u32_to_f64_cvt(u32 h) { return __uint2double_rn(h); } // I2F.F64.U32 (conversion pipe), exact
-#ifndef GLB_CVT_I2F
-#define GLB_CVT_I2F 0
-#endif
-// which == 0: low half of a word, 1: high half
-template <int WHICH> __device__ __forceinline__ double u32_to_f64(u32 h)
-{
-    if (GLB_CVT_I2F == 1 || (GLB_CVT_I2F == 2 && WHICH == 1)) return u32_to_f64_cvt(h);
-    return u32_to_f64_pair(h);
-}
+__device__ __forceinline__ double u32_to_f64(u32 h) { return __uint2double_rn(h); }
 
 constexpr double kTwo52 = 4503599627370496.0;
 constexpr u64 kTwo52Bits = 0x4330000000000000ULL;
@@ -81,8 +73,8 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
     double lo[12], hi[12];
 #pragma unroll
     for (int j = 0; j < 12; j++) {
-        lo[j] = u32_to_f64<0>((u32)s[j]);
-        hi[j] = u32_to_f64<1>((u32)(s[j] >> 32));
+        lo[j] = u32_to_f64((u32)s[j]);
+        hi[j] = u32_to_f64((u32)(s[j] >> 32));
     }
 #pragma unroll
     for (int i = 0; i < NOUT; i++) {
@@ -118,8 +110,8 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
     double lo[12], hi[12];
 #pragma unroll
     for (int j = 0; j < 12; j++) {
-        lo[j] = u32_to_f64<0>((u32)s[j]);
-        hi[j] = u32_to_f64<1>((u32)(s[j] >> 32));
+        lo[j] = u32_to_f64((u32)s[j]);
+        hi[j] = u32_to_f64((u32)(s[j] >> 32));
     }
     u64 x;
     {
@@ -135,7 +127,7 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
     }
     const u64 y = sbox_add(x, c_next);
     const u64 d = gl::sub(y, x);
-    const double dlo = u32_to_f64<0>((u32)d), dhi = u32_to_f64<1>((u32)(d >> 32));
+    const double dlo = u32_to_f64((u32)d), dhi = u32_to_f64((u32)(d >> 32));
 #pragma unroll
     for (int i = 0; i < 12; i++) {
         double dl = kTwo52 + (double)(DM & 0xFFFFFFFFu), dh = kTwo52 + (double)(DM >> 32);
