@@ -65,6 +65,67 @@ constexpr u64 kTwo52Bits = 0x4330000000000000ULL;
 // -(x) mod p for a 128-bit x (compile time)
 __host__ __device__ constexpr u64 neg_mod_p(unsigned __int128 x) { return (u64)((gl::P - (u64)(x % gl::P)) % gl::P); }
 
+#ifndef GLB_MDS_SPLIT
+#define GLB_MDS_SPLIT 1 // 0: plain 12 x 12 form of every layer (kept for A/B runs of tools/ubench)
+#endif
+// ---- split-circulant evaluation -----------------------------------------------------------------------------------
+// new = c (*) old + 8 old[0] e_0 with c the MDS circulant (cyclic convolution of length 12).  By the CRT on
+// x^12 - 1 = (x^6 - 1)(x^6 + 1) the product is a cyclic product of length 6 on (v_lo + v_hi) and a negacyclic one on
+// (v_lo - v_hi); c_lo +- c_hi is even, so the halved coefficients are integers and
+//     y[k] = P_k + N_k,  y[k+6] = P_k - N_k,   P_k = sum_a cp[(k-a) mod 6] vp[a],  N_k = sum_a +-cm[(k-a) mod 6] vm[a]:
+// 72 multiply-adds + 24 additions per 32-bit half instead of 144 (tests/test_poseidon_dense_form.py proves the identity
+// and the < 2^53 bounds with exact integers).  The same holds for the circulant part c (*) c of the squared matrix.
+__host__ __device__ constexpr int circ12(int k)
+{
+    constexpr int circ[12] = {17, 20, 34, 18, 39, 13, 13, 28, 2, 16, 41, 15};
+    return circ[k % 12];
+}
+__host__ __device__ constexpr int circ12sq(int k) // (c (*) c)[k]
+{
+    int acc = 0;
+    for (int a = 0; a < 12; a++) acc += circ12(a) * circ12((k - a + 12) % 12);
+    return acc;
+}
+struct CircM {  // the MDS circulant
+    static __host__ __device__ constexpr int c(int k) { return circ12(k); }
+};
+struct CircM2 { // circulant part of the squared matrix
+    static __host__ __device__ constexpr int c(int k) { return circ12sq(k); }
+};
+template <class K> __host__ __device__ constexpr bool circ_halves_even()
+{
+    for (int k = 0; k < 6; k++)
+        if ((K::c(k) + K::c(k + 6)) % 2 != 0) return false;
+    return true;
+}
+static_assert(circ_halves_even<CircM>() && circ_halves_even<CircM2>(), "halved circulant coefficients must be integers");
+
+// vp/vm of one 32-bit half plane
+__device__ __forceinline__ void split_pm(const double (&v)[12], double (&vp)[6], double (&vm)[6])
+{
+#pragma unroll
+    for (int a = 0; a < 6; a++) {
+        vp[a] = v[a] + v[a + 6];
+        vm[a] = v[a] - v[a + 6];
+    }
+}
+// P_k (started at `bias`) and N_k of output pair (k, k+6)
+template <class K, int k>
+__device__ __forceinline__ void cyc_pair(const double (&vp)[6], const double (&vm)[6], double bias, double &P, double &N)
+{
+    P = bias;
+#pragma unroll
+    for (int a = 0; a < 6; a++) {
+        const int idx = (k - a + 6) % 6;
+        const double cp = (double)((K::c(idx) + K::c(idx + 6)) / 2);
+        const double cm = (double)((a <= k ? 1 : -1) * ((K::c(idx) - K::c(idx + 6)) / 2));
+        P = fma(cp, vp[a], P);
+        N = a == 0 ? cm * vm[0] : fma(cm, vm[a], N);
+    }
+}
+
+template <int V> struct KTag { static constexpr int value = V; };
+
 template <int NOUT = 12>
 __device__ __forceinline__ void mds_layer(u64 (&s)[12])
 {
@@ -76,17 +137,44 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
         lo[j] = u32_to_f64((u32)s[j]);
         hi[j] = u32_to_f64((u32)(s[j] >> 32));
     }
+    if constexpr (NOUT == 12 && GLB_MDS_SPLIT != 0) {
+        const double lo0 = lo[0], hi0 = hi[0];
+        double lp[6], lm[6], hp[6], hm[6];
+        split_pm(lo, lp, lm);
+        split_pm(hi, hp, hm);
+        auto emit = [&](auto ktag) {
+            constexpr int k = decltype(ktag)::value;
+            double pl, nl, ph, nh;
+            cyc_pair<CircM, k>(lp, lm, kTwo52 + (double)(DM & 0xFFFFFFFFu), pl, nl);
+            cyc_pair<CircM, k>(hp, hm, kTwo52 + (double)(DM >> 32), ph, nh);
+            double a_l = pl + nl, a_h = ph + nh;
+            const double b_l = pl - nl, b_h = ph - nh;
+            if (k == 0) { a_l = fma(8.0, lo0, a_l); a_h = fma(8.0, hi0, a_h); } // the +8 on M[0][0]
+            {
+                const u64 L = (u64)__double_as_longlong(a_l), H = (u64)__double_as_longlong(a_h);
+                const u64 t = (L >> 32) + H;
+                s[k] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+            }
+            {
+                const u64 L = (u64)__double_as_longlong(b_l), H = (u64)__double_as_longlong(b_h);
+                const u64 t = (L >> 32) + H;
+                s[k + 6] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+            }
+        };
+        emit(KTag<0>()); emit(KTag<1>()); emit(KTag<2>()); emit(KTag<3>()); emit(KTag<4>()); emit(KTag<5>());
+    } else {
 #pragma unroll
-    for (int i = 0; i < NOUT; i++) {
-        double dl = kTwo52 + (double)(DM & 0xFFFFFFFFu), dh = kTwo52 + (double)(DM >> 32);
+        for (int i = 0; i < NOUT; i++) {
+            double dl = kTwo52 + (double)(DM & 0xFFFFFFFFu), dh = kTwo52 + (double)(DM >> 32);
 #pragma unroll
-        for (int j = 0; j < 12; j++) {
-            dl = fma((double)mds_entry(j, i), lo[j], dl);
-            dh = fma((double)mds_entry(j, i), hi[j], dh);
+            for (int j = 0; j < 12; j++) {
+                dl = fma((double)mds_entry(j, i), lo[j], dl);
+                dh = fma((double)mds_entry(j, i), hi[j], dh);
+            }
+            const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh); // raw: bias included
+            const u64 t = (L >> 32) + H; // < 2^64
+            s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
         }
-        const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh); // raw: bias included
-        const u64 t = (L >> 32) + H; // < 2^64
-        s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
     }
 }
 
@@ -128,6 +216,36 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
     const u64 y = sbox_add(x, c_next);
     const u64 d = gl::sub(y, x);
     const double dlo = u32_to_f64((u32)d), dhi = u32_to_f64((u32)(d >> 32));
+#if GLB_MDS_SPLIT
+    {
+        // (M M) a + d M[0][.]  =  (c (*) c) (*) a + (8 a_0 + d) c + 8 (x + d) e_0, and x + d = y (mod p): per 32-bit half
+        const double wl = fma(8.0, lo[0], dlo), wh = fma(8.0, hi[0], dhi);
+        const double yl8 = 8.0 * u32_to_f64((u32)y), yh8 = 8.0 * u32_to_f64((u32)(y >> 32));
+        double lp[6], lm[6], hp[6], hm[6];
+        split_pm(lo, lp, lm);
+        split_pm(hi, hp, hm);
+        auto emit = [&](auto ktag) {
+            constexpr int k = decltype(ktag)::value;
+            double pl, nl, ph, nh;
+            cyc_pair<CircM2, k>(lp, lm, kTwo52 + (double)(DM & 0xFFFFFFFFu), pl, nl);
+            cyc_pair<CircM2, k>(hp, hm, kTwo52 + (double)(DM >> 32), ph, nh);
+            double a_l = fma((double)circ12(k), wl, pl + nl), a_h = fma((double)circ12(k), wh, ph + nh);
+            const double b_l = fma((double)circ12(k + 6), wl, pl - nl), b_h = fma((double)circ12(k + 6), wh, ph - nh);
+            if (k == 0) { a_l += yl8; a_h += yh8; }
+            {
+                const u64 L = (u64)__double_as_longlong(a_l), H = (u64)__double_as_longlong(a_h);
+                const u64 t = (L >> 32) + H;
+                s[k] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+            }
+            {
+                const u64 L = (u64)__double_as_longlong(b_l), H = (u64)__double_as_longlong(b_h);
+                const u64 t = (L >> 32) + H;
+                s[k + 6] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+            }
+        };
+        emit(KTag<0>()); emit(KTag<1>()); emit(KTag<2>()); emit(KTag<3>()); emit(KTag<4>()); emit(KTag<5>());
+    }
+#else
 #pragma unroll
     for (int i = 0; i < 12; i++) {
         double dl = kTwo52 + (double)(DM & 0xFFFFFFFFu), dh = kTwo52 + (double)(DM >> 32);
@@ -142,6 +260,7 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
         const u64 t = (L >> 32) + H; // < 2^64
         s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
     }
+#endif
 }
 
 // Full permutation.  Input: any representatives; output: lazily reduced.  OUT4: only s[0..4) of the result

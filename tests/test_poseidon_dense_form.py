@@ -102,3 +102,81 @@ def test_fp64_exactness_bounds():
     worst2 = max(sum(M2(j, i) for j in range(12)) + M(0, i) for i in range(12))
     assert (1 << 52) + (1 << 32) + worst1 * (2**32 - 1) < (1 << 53)
     assert (1 << 52) + (1 << 32) + worst2 * (2**32 - 1) < (1 << 53)
+
+
+# ---- the split-circulant evaluation of the MDS layers (csrc/poseidon.cuh: cyc12_pair) -----------------------------------
+# c (*) v mod x^12 - 1 = CRT of a cyclic product mod x^6 - 1 on (v_lo + v_hi) and a negacyclic product mod x^6 + 1 on
+# (v_lo - v_hi); the halved coefficient vectors are integers because c_lo +- c_hi is even.
+def _cyc(c, v):
+    n = len(c)
+    return [sum(c[(k - a) % n] * v[a] for a in range(n)) for k in range(n)]
+
+
+C2 = _cyc(CIRC, CIRC)  # circulant part of the squared matrix
+
+
+def _split_cyc12(c, v):
+    assert all((c[k] + c[k + 6]) % 2 == 0 for k in range(6))
+    cp = [(c[k] + c[k + 6]) // 2 for k in range(6)]
+    cm = [(c[k] - c[k + 6]) // 2 for k in range(6)]
+    vp = [v[a] + v[a + 6] for a in range(6)]
+    vm = [v[a] - v[a + 6] for a in range(6)]
+    y = [0] * 12
+    worst = 0
+    for k in range(6):
+        pk = sum(cp[(k - a) % 6] * vp[a] for a in range(6))
+        nk = sum((1 if a <= k else -1) * cm[(k - a) % 6] * vm[a] for a in range(6))
+        worst = max(worst, pk, abs(nk))
+        y[k], y[k + 6] = pk + nk, pk - nk
+    return y, worst
+
+
+def test_split_circulant_layer_is_the_mds_layer():
+    rng = random.Random(11)
+    for _ in range(50):
+        # 32-bit halves, as the kernel feeds them
+        v = [rng.choice([0, 1, 2**32 - 1, rng.randrange(2**32)]) for _ in range(12)]
+        y, worst = _split_cyc12(CIRC, v)
+        y[0] += 8 * v[0]
+        assert y == [sum(M(j, i) * v[j] for j in range(12)) for i in range(12)]
+        assert (1 << 52) + (1 << 32) + worst < (1 << 53) and max(y) + (1 << 52) + (1 << 32) < (1 << 53)
+
+
+def test_split_circulant_pair_layer():
+    """(M M) a + d M[0][.]  ==  c2 (*) a + (8 a_0 + d) c + 8 (x + d) e_0  with x = <M[.][0], a>, on 32-bit halves."""
+    rng = random.Random(12)
+    assert all((C2[k] + C2[k + 6]) % 2 == 0 for k in range(6))
+    for _ in range(50):
+        a = [rng.choice([0, 2**32 - 1, rng.randrange(2**32)]) for _ in range(12)]
+        d = rng.choice([0, 2**32 - 1, rng.randrange(2**32)])
+        x = sum(M(j, 0) * a[j] for j in range(12))
+        want = [sum(M2(j, i) * a[j] for j in range(12)) + M(0, i) * d for i in range(12)]
+        y, worst = _split_cyc12(C2, a)
+        w = 8 * a[0] + d
+        got = [y[i] + CIRC[i] * w for i in range(12)]
+        got[0] += 8 * (x + d)
+        assert got == want
+        assert (1 << 52) + (1 << 32) + worst + 64 * w + 8 * (x + d) < (1 << 53)
+
+
+def test_split_circulant_pair_layer_mod_p_with_y():
+    """What the kernel does: 8 (x + d) e_0 is replaced by 8 y e_0 (y = x^7 + c = x + d mod p), per 32-bit half."""
+    rng = random.Random(13)
+    for _ in range(40):
+        a = [rng.randrange(2**64) for _ in range(12)]                       # any representatives
+        cn = rng.randrange(P)
+        x = sum(M(j, 0) * a[j] for j in range(12)) % P
+        y = (sb(x) + cn) % P
+        d = (y - x) % P
+        want = [(sum(M2(j, i) * a[j] for j in range(12)) + M(0, i) * d) % P for i in range(12)]
+
+        def half(sel):
+            ah, dh, yh = [sel(v) for v in a], sel(d), sel(y)
+            out, _ = _split_cyc12(C2, ah)
+            w = 8 * ah[0] + dh
+            out = [out[i] + CIRC[i] * w for i in range(12)]
+            out[0] += 8 * yh
+            assert 0 <= min(out) and max(out) + (1 << 52) + (1 << 32) < (1 << 53)
+            return out
+        lo, hi = half(lambda v: v & 0xFFFFFFFF), half(lambda v: v >> 32)
+        assert [(lo[i] + (hi[i] << 32)) % P for i in range(12)] == want
