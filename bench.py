@@ -248,21 +248,24 @@ def main():
     leaf_bytes = e * ncols * 8 + e * 32                 # read the extended matrix once, write the digests
     lde_bytes, lde_passes = lde_pass_bytes(logn, loge, ncols)
     sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
-    # ncu (profiles/r1_18_leaf_ncu_paired_rounds.txt): 16,137 warp instructions per permutation in k_linear_hash_rows (6,272 of
-    # them DFMA/DADD: the MDS layers, one per full round and one per PAIR of partial rounds); 0.60 instructions issued per
-    # clock per SM sub-partition with the fmaheavy (IMAD) pipe 56 % and the FP64 pipe 46 % busy; DRAM traffic 1.003x the
-    # algorithmic bytes (4.376 GB moved for 4.362 GB on the 2^21 x 256 capture; a c2 launch is too long to replay)
-    INSTR_PER_PERM, TRAFFIC_RATIO, NCU_IPC, NCU_FMAHEAVY, NCU_FP64 = 16137.0, 1.003, 0.60, 0.565, 0.463
+    # ncu (profiles/r1_24_leaf_ncu_split_circulant.txt): 13,833 warp instructions per permutation in k_linear_hash_rows (4,082 of
+    # them DFMA/DADD/DMUL: the split-circulant MDS layers, one per full round and one per PAIR of partial rounds); 0.59
+    # instructions issued per clock per SM sub-partition with the fmaheavy (IMAD) pipe 63 % and the FP64 pipe 35 % busy -- the two
+    # do not overlap in this instruction mix, their busy fractions add up to ~1; DRAM traffic 1.003x the algorithmic bytes
+    # (4.376 GB moved for 4.362 GB on the 2^21 x 256 capture; a c2 launch is too long to replay)
+    INSTR_PER_PERM, TRAFFIC_RATIO, NCU_IPC, NCU_FMAHEAVY, NCU_FP64 = 13833.0, 1.003, 0.59, 0.630, 0.345
     ipc = leaf_perm / (phase["leaf_ms"] / 1e3) / 32 * INSTR_PER_PERM / (148 * 4 * sm_hz)
-    cap = min(1.0, NCU_IPC / max(NCU_FMAHEAVY, NCU_FP64))  # issue rate at which the busier pipe (or the issue slot) saturates
+    # observed in three captures (r1_18, r1_22, r1_24): fmaheavy-busy + FP64-busy = 1.01, 1.01, 0.98 -- in this instruction mix the
+    # two pipes take turns instead of overlapping, so the issue rate saturates where their SUM reaches 1
+    cap = min(1.0, NCU_IPC / (NCU_FMAHEAVY + NCU_FP64))
     roofline = {"kernel": "poseidon::k_linear_hash_rows (leaf hashing, %.0f%% of the step)" % (100 * phase["leaf_ms"] / dev_ms),
                 "bound": "hbm", "achieved": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9 / hbm_peak, "traffic": leaf_bytes * TRAFFIC_RATIO,
-                "traffic_source": "dram__bytes_read+write of the same kernel captured with ncu --set full on the 2^21 x 256 shape (profiles/r1_18_leaf_ncu_paired_rounds.txt), scaled by bytes",
+                "traffic_source": "dram__bytes_read+write of the same kernel captured with ncu --set full on the 2^21 x 256 shape (profiles/r1_24_leaf_ncu_split_circulant.txt), scaled by bytes",
                 "peak_source": peak_src,
                 "note": "the kernel is bound by instruction issue across the integer and FP64 pipes, not HBM: %.3f G Poseidon permutations/s = "
-                        "%.2f warp instr/clk/SMSP (ncu: 16.14 k instr per permutation, fmaheavy pipe 56%% busy, FP64 pipe 46%% busy with the "
-                        "exact-integer MDS layers); the issue slot saturates at %.2f instr/clk/SMSP" % (leaf_perm / phase["leaf_ms"] / 1e6, ipc, cap),
+                        "%.2f warp instr/clk/SMSP (ncu: 13.83 k instr per permutation, fmaheavy pipe 63%% busy, FP64 pipe 35%% busy with the "
+                        "exact-integer MDS layers, and the two busy fractions add up: the pipes alternate); that mix saturates at %.2f instr/clk/SMSP" % (leaf_perm / phase["leaf_ms"] / 1e6, ipc, cap),
                 "issue": {"warp_instr_per_clk_per_smsp": ipc, "model_cap": cap, "frac_of_model": ipc / cap}}
     epasses = (n * (1 if logn <= 8 else (logn + 7) // 8) + e * (1 if loge <= 8 else (loge + 7) // 8)) * ncols
     phases = {
