@@ -66,7 +66,7 @@ constexpr u64 kTwo52Bits = 0x4330000000000000ULL;
 __host__ __device__ constexpr u64 neg_mod_p(unsigned __int128 x) { return (u64)((gl::P - (u64)(x % gl::P)) % gl::P); }
 
 #ifndef GLB_MDS_SPLIT
-#define GLB_MDS_SPLIT 1 // 0: plain 12 x 12 form of every layer (kept for A/B runs of tools/ubench)
+#define GLB_MDS_SPLIT 2 // 2: two CRT levels (default); 1: one level; 0: plain 12 x 12 form (1554 / 1398 M perm/s against 1584: kept for A/B runs of tools/ubench)
 #endif
 // ---- split-circulant evaluation -----------------------------------------------------------------------------------
 // new = c (*) old + 8 old[0] e_0 with c the MDS circulant (cyclic convolution of length 12).  By the CRT on
@@ -124,6 +124,60 @@ __device__ __forceinline__ void cyc_pair(const double (&vp)[6], const double (&v
     }
 }
 
+// ---- GLB_MDS_SPLIT >= 2 (default): a second CRT level on the cyclic half, x^6 - 1 = (x^3 - 1)(x^3 + 1):
+// P_k = PP_k + PN_k, P_{k+3} = PP_k - PN_k with a cyclic / negacyclic product of length 3 on vp_lo +- vp_hi -- 30 instead
+// of 36 operations per half plane (tests/test_poseidon_dense_form.py::test_two_level_split_equals_one_level).
+template <class K> __host__ __device__ constexpr int circ_cp(int i) { return (K::c(i % 6) + K::c(i % 6 + 6)) / 2; }
+template <class K> __host__ __device__ constexpr bool circ_quarters_even()
+{
+    for (int k = 0; k < 3; k++)
+        if ((circ_cp<K>(k) + circ_cp<K>(k + 3)) % 2 != 0) return false;
+    return true;
+}
+static_assert(circ_quarters_even<CircM>() && circ_quarters_even<CircM2>(), "quartered circulant coefficients must be integers");
+__device__ __forceinline__ void split_pm3(const double (&vp)[6], double (&vpp)[3], double (&vpm)[3])
+{
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        vpp[a] = vp[a] + vp[a + 3];
+        vpm[a] = vp[a] - vp[a + 3];
+    }
+}
+template <class K, int k> // k < 3
+__device__ __forceinline__ void cyc_p2(const double (&vpp)[3], const double (&vpm)[3], double bias, double &Pk, double &Pk3)
+{
+    double pp = bias, pn = 0.0;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const int idx = (k - a + 3) % 3;
+        const double cpp = (double)((circ_cp<K>(idx) + circ_cp<K>(idx + 3)) / 2);
+        const double cpm = (double)((a <= k ? 1 : -1) * ((circ_cp<K>(idx) - circ_cp<K>(idx + 3)) / 2));
+        pp = fma(cpp, vpp[a], pp);
+        pn = a == 0 ? cpm * vpm[0] : fma(cpm, vpm[a], pn);
+    }
+    Pk = pp + pn;
+    Pk3 = pp - pn;
+}
+template <class K, int k> // k < 6
+__device__ __forceinline__ double cyc_n(const double (&vm)[6])
+{
+    double N = 0.0;
+#pragma unroll
+    for (int a = 0; a < 6; a++) {
+        const int idx = (k - a + 6) % 6;
+        const double cm = (double)((a <= k ? 1 : -1) * ((K::c(idx) - K::c(idx + 6)) / 2));
+        N = a == 0 ? cm * vm[0] : fma(cm, vm[a], N);
+    }
+    return N;
+}
+// (L, H) raw biased sums -> word
+__device__ __forceinline__ u64 fold_lh(double l, double h)
+{
+    const u64 L = (u64)__double_as_longlong(l), H = (u64)__double_as_longlong(h);
+    const u64 t = (L >> 32) + H;
+    return gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+}
+
 template <int V> struct KTag { static constexpr int value = V; };
 
 template <int NOUT = 12>
@@ -137,7 +191,28 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
         lo[j] = u32_to_f64((u32)s[j]);
         hi[j] = u32_to_f64((u32)(s[j] >> 32));
     }
-    if constexpr (NOUT == 12 && GLB_MDS_SPLIT != 0) {
+    if constexpr (NOUT == 12 && GLB_MDS_SPLIT >= 2) {
+        const double lo0 = lo[0], hi0 = hi[0];
+        double lp[6], lm[6], hp[6], hm[6], lpp[3], lpm[3], hpp[3], hpm[3];
+        split_pm(lo, lp, lm);
+        split_pm(hi, hp, hm);
+        split_pm3(lp, lpp, lpm);
+        split_pm3(hp, hpp, hpm);
+        auto emit = [&](auto ktag) { // outputs k, k+3, k+6, k+9
+            constexpr int k = decltype(ktag)::value;
+            double pl, pl3, ph, ph3;
+            cyc_p2<CircM, k>(lpp, lpm, kTwo52 + (double)(DM & 0xFFFFFFFFu), pl, pl3);
+            cyc_p2<CircM, k>(hpp, hpm, kTwo52 + (double)(DM >> 32), ph, ph3);
+            const double nl = cyc_n<CircM, k>(lm), nh = cyc_n<CircM, k>(hm), nl3 = cyc_n<CircM, k + 3>(lm), nh3 = cyc_n<CircM, k + 3>(hm);
+            double a_l = pl + nl, a_h = ph + nh;
+            if (k == 0) { a_l = fma(8.0, lo0, a_l); a_h = fma(8.0, hi0, a_h); }
+            s[k] = fold_lh(a_l, a_h);
+            s[k + 6] = fold_lh(pl - nl, ph - nh);
+            s[k + 3] = fold_lh(pl3 + nl3, ph3 + nh3);
+            s[k + 9] = fold_lh(pl3 - nl3, ph3 - nh3);
+        };
+        emit(KTag<0>()); emit(KTag<1>()); emit(KTag<2>());
+    } else if constexpr (NOUT == 12 && GLB_MDS_SPLIT != 0) {
         const double lo0 = lo[0], hi0 = hi[0];
         double lp[6], lm[6], hp[6], hm[6];
         split_pm(lo, lp, lm);
@@ -216,7 +291,31 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
     const u64 y = sbox_add(x, c_next);
     const u64 d = gl::sub(y, x);
     const double dlo = u32_to_f64((u32)d), dhi = u32_to_f64((u32)(d >> 32));
-#if GLB_MDS_SPLIT
+#if GLB_MDS_SPLIT >= 2
+    {
+        const double wl = fma(8.0, lo[0], dlo), wh = fma(8.0, hi[0], dhi);
+        const double yl8 = 8.0 * u32_to_f64((u32)y), yh8 = 8.0 * u32_to_f64((u32)(y >> 32));
+        double lp[6], lm[6], hp[6], hm[6], lpp[3], lpm[3], hpp[3], hpm[3];
+        split_pm(lo, lp, lm);
+        split_pm(hi, hp, hm);
+        split_pm3(lp, lpp, lpm);
+        split_pm3(hp, hpp, hpm);
+        auto emit = [&](auto ktag) { // outputs k, k+3, k+6, k+9
+            constexpr int k = decltype(ktag)::value;
+            double pl, pl3, ph, ph3;
+            cyc_p2<CircM2, k>(lpp, lpm, kTwo52 + (double)(DM & 0xFFFFFFFFu), pl, pl3);
+            cyc_p2<CircM2, k>(hpp, hpm, kTwo52 + (double)(DM >> 32), ph, ph3);
+            const double nl = cyc_n<CircM2, k>(lm), nh = cyc_n<CircM2, k>(hm), nl3 = cyc_n<CircM2, k + 3>(lm), nh3 = cyc_n<CircM2, k + 3>(hm);
+            double a_l = fma((double)circ12(k), wl, pl + nl), a_h = fma((double)circ12(k), wh, ph + nh);
+            if (k == 0) { a_l += yl8; a_h += yh8; }
+            s[k] = fold_lh(a_l, a_h);
+            s[k + 6] = fold_lh(fma((double)circ12(k + 6), wl, pl - nl), fma((double)circ12(k + 6), wh, ph - nh));
+            s[k + 3] = fold_lh(fma((double)circ12(k + 3), wl, pl3 + nl3), fma((double)circ12(k + 3), wh, ph3 + nh3));
+            s[k + 9] = fold_lh(fma((double)circ12(k + 9), wl, pl3 - nl3), fma((double)circ12(k + 9), wh, ph3 - nh3));
+        };
+        emit(KTag<0>()); emit(KTag<1>()); emit(KTag<2>());
+    }
+#elif GLB_MDS_SPLIT
     {
         // (M M) a + d M[0][.]  =  (c (*) c) (*) a + (8 a_0 + d) c + 8 (x + d) e_0, and x + d = y (mod p): per 32-bit half
         const double wl = fma(8.0, lo[0], dlo), wh = fma(8.0, hi[0], dhi);

@@ -180,3 +180,39 @@ def test_split_circulant_pair_layer_mod_p_with_y():
             return out
         lo, hi = half(lambda v: v & 0xFFFFFFFF), half(lambda v: v >> 32)
         assert [(lo[i] + (hi[i] << 32)) % P for i in range(12)] == want
+
+
+# ---- second CRT level on the cyclic half (GLB_MDS_SPLIT=2 in csrc/poseidon.cuh): x^6 - 1 = (x^3 - 1)(x^3 + 1) ---------------
+def _split2_cyc12(c, v):
+    cp = [(c[k] + c[k + 6]) // 2 for k in range(6)]
+    cm = [(c[k] - c[k + 6]) // 2 for k in range(6)]
+    assert all((cp[k] + cp[k + 3]) % 2 == 0 for k in range(3))
+    cpp = [(cp[k] + cp[k + 3]) // 2 for k in range(3)]
+    cpm = [(cp[k] - cp[k + 3]) // 2 for k in range(3)]
+    vp = [v[a] + v[a + 6] for a in range(6)]
+    vm = [v[a] - v[a + 6] for a in range(6)]
+    vpp = [vp[a] + vp[a + 3] for a in range(3)]
+    vpm = [vp[a] - vp[a + 3] for a in range(3)]
+    pk = [0] * 6
+    worst = 0
+    for k in range(3):
+        pp = sum(cpp[(k - a) % 3] * vpp[a] for a in range(3))
+        pn = sum((1 if a <= k else -1) * cpm[(k - a) % 3] * vpm[a] for a in range(3))
+        pk[k], pk[k + 3] = pp + pn, pp - pn
+        worst = max(worst, pp, abs(pn))
+    y = [0] * 12
+    for k in range(6):
+        nk = sum((1 if a <= k else -1) * cm[(k - a) % 6] * vm[a] for a in range(6))
+        y[k], y[k + 6] = pk[k] + nk, pk[k] - nk
+        worst = max(worst, pk[k], abs(nk))
+    return y, worst
+
+
+def test_two_level_split_equals_one_level():
+    rng = random.Random(14)
+    for c in (CIRC, C2):
+        for _ in range(40):
+            v = [rng.choice([0, 2**32 - 1, rng.randrange(2**32)]) for _ in range(12)]
+            y2, worst = _split2_cyc12(c, v)
+            assert y2 == _cyc(c, v)
+            assert (1 << 52) + (1 << 32) + worst < (1 << 53)
