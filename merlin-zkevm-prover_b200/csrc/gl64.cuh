@@ -130,6 +130,54 @@ __device__ __forceinline__ u64 reduce160(u32 x0, u32 x1, u32 x2, u32 x3, u32 x4)
     return pack(r0, r1);
 }
 
+// ---- ALU-only forms of the two reductions (no IMAD.WIDE for the x2 * (2^32 - 1) term): x2 * (2^32 - 1) = x2 * 2^32 - x2, so
+//   {x0,x1} + x2 (2^32 - 1) - x3 = {x0, x1 + x2} - (x2 + x3), again with one net correction k = carry - borrow.
+// Three more instructions than reduce128 / four more than reduce96, but all on the ALU pipe.  NOT used by default: they are
+// the round-2 experiment for the Poseidon kernels, where ncu shows the FP64 pipe and the IMAD pipe taking turns while the ALU
+// pipe is 36 % busy (profiles/r1_27_ubench_fp64_phase.txt); tests/test_reduction_forms.py checks the carry logic exhaustively
+// on edge values and on random inputs with an exact simulation.
+__device__ __forceinline__ u64 reduce128_alu(u128 x)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 h, c1, s0, s1, b, k, kl, kh;\n\t"
+        "add.cc.u32 h, %3, %4;\n\t"
+        "addc.u32 c1, 0, 0;\n\t"
+        "add.cc.u32 s0, %4, %5;\n\t"
+        "addc.u32 s1, 0, 0;\n\t"
+        "sub.cc.u32 %0, %2, s0;\n\t"
+        "subc.cc.u32 %1, h, s1;\n\t"
+        "subc.u32 b, 0, 0;\n\t"                      // b = -borrow
+        "add.u32 k, c1, b;\n\t"                      // k = carry - borrow
+        "neg.s32 kl, k;\n\t"
+        "shr.s32 kh, k, 31;\n\t"
+        "add.cc.u32 %0, %0, kl;\n\t"                 // r += k*(2^32-1)
+        "addc.u32 %1, %1, kh;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(x.x0), "r"(x.x1), "r"(x.x2), "r"(x.x3));
+    return pack(r0, r1);
+}
+__device__ __forceinline__ u64 reduce96_alu(u32 x0, u32 x1, u32 x2)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 h, c1, b, k;\n\t"
+        "add.cc.u32 h, %3, %4;\n\t"
+        "addc.u32 c1, 0, 0;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\t"
+        "subc.cc.u32 %1, h, 0;\n\t"
+        "subc.u32 b, 0, 0;\n\t"
+        "add.u32 k, c1, b;\n\t"                      // 0 or 1
+        "neg.s32 k, k;\n\t"                          // 0 or 0xFFFFFFFF
+        "add.cc.u32 %0, %0, k;\n\t"
+        "addc.u32 %1, %1, 0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(x0), "r"(x1), "r"(x2));
+    return pack(r0, r1);
+}
+
 // nvcc's native 128-bit product is one instruction shorter than mul_wide (the cross-term carry rides
 // on IMAD.WIDE.U32.X instead of a SEL): 4 IMAD.WIDE + 3 ALU, then the 8-instruction reduction.
 __device__ __forceinline__ u128 mul_wide_native(u64 a, u64 b)
@@ -143,6 +191,10 @@ __device__ __forceinline__ u64 mul(u64 a, u64 b) { return reduce128(mul_wide_nat
 __device__ __forceinline__ u64 sqr(u64 a) { return reduce128(mul_wide_native(a, a)); }
 // a*b + c  (fused: the addend rides on the first partial product)
 __device__ __forceinline__ u64 mad(u64 a, u64 b, u64 c) { return reduce128(mad_wide(a, b, c)); }
+// the same three with the ALU-only reduction (round-2 experiment, see reduce128_alu)
+__device__ __forceinline__ u64 mul_alu(u64 a, u64 b) { return reduce128_alu(mul_wide_native(a, b)); }
+__device__ __forceinline__ u64 sqr_alu(u64 a) { return reduce128_alu(mul_wide_native(a, a)); }
+__device__ __forceinline__ u64 mad_alu(u64 a, u64 b, u64 c) { return reduce128_alu(mad_wide(a, b, c)); }
 
 // a + b for arbitrary representatives.  Two possible wraps (reference add: scalar.hpp:16-35).
 __device__ __forceinline__ u64 add(u64 a, u64 b)

@@ -40,13 +40,31 @@ __device__ __forceinline__ constexpr u32 mds_entry(int j, int i)
     return circ[(i - j + 12) % 12] + ((i == 0 && j == 0) ? 8u : 0u);
 }
 
+#ifndef GLB_POSEIDON_RED_ALU
+#define GLB_POSEIDON_RED_ALU 0 // round-2 experiment: 1 = S-box reductions, 2 = also the 96-bit reductions of the MDS layers, in ALU-only form
+#endif
 // x^7 + c   (c any representative)
 __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
 {
+#if GLB_POSEIDON_RED_ALU
+    u64 x2 = gl::sqr_alu(x);
+    u64 x3 = gl::mul_alu(x, x2);
+    u64 x4 = gl::sqr_alu(x2);
+    return gl::mad_alu(x3, x4, c);
+#else
     u64 x2 = gl::sqr(x);
     u64 x3 = gl::mul(x, x2);
     u64 x4 = gl::sqr(x2);
     return gl::mad(x3, x4, c);
+#endif
+}
+__device__ __forceinline__ u64 red96(u32 x0, u32 x1, u32 x2)
+{
+#if GLB_POSEIDON_RED_ALU >= 2
+    return gl::reduce96_alu(x0, x1, x2);
+#else
+    return gl::reduce96(x0, x1, x2);
+#endif
 }
 
 // new[i] = sum_j M[j][i] old[j]  (poseidon_goldilocks.hpp:148-162).  Entries < 64, so the sums of
@@ -175,7 +193,7 @@ __device__ __forceinline__ u64 fold_lh(double l, double h)
 {
     const u64 L = (u64)__double_as_longlong(l), H = (u64)__double_as_longlong(h);
     const u64 t = (L >> 32) + H;
-    return gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+    return red96((u32)L, (u32)t, (u32)(t >> 32));
 }
 
 template <int V> struct KTag { static constexpr int value = V; };
@@ -228,12 +246,12 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
             {
                 const u64 L = (u64)__double_as_longlong(a_l), H = (u64)__double_as_longlong(a_h);
                 const u64 t = (L >> 32) + H;
-                s[k] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+                s[k] = red96((u32)L, (u32)t, (u32)(t >> 32));
             }
             {
                 const u64 L = (u64)__double_as_longlong(b_l), H = (u64)__double_as_longlong(b_h);
                 const u64 t = (L >> 32) + H;
-                s[k + 6] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+                s[k + 6] = red96((u32)L, (u32)t, (u32)(t >> 32));
             }
         };
         emit(KTag<0>()); emit(KTag<1>()); emit(KTag<2>()); emit(KTag<3>()); emit(KTag<4>()); emit(KTag<5>());
@@ -248,7 +266,7 @@ __device__ __forceinline__ void mds_layer(u64 (&s)[12])
             }
             const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh); // raw: bias included
             const u64 t = (L >> 32) + H; // < 2^64
-            s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+            s[i] = red96((u32)L, (u32)t, (u32)(t >> 32));
         }
     }
 }
@@ -286,7 +304,7 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
         }
         const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh);
         const u64 t = (L >> 32) + H;
-        x = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+        x = red96((u32)L, (u32)t, (u32)(t >> 32));
     }
     const u64 y = sbox_add(x, c_next);
     const u64 d = gl::sub(y, x);
@@ -334,12 +352,12 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
             {
                 const u64 L = (u64)__double_as_longlong(a_l), H = (u64)__double_as_longlong(a_h);
                 const u64 t = (L >> 32) + H;
-                s[k] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+                s[k] = red96((u32)L, (u32)t, (u32)(t >> 32));
             }
             {
                 const u64 L = (u64)__double_as_longlong(b_l), H = (u64)__double_as_longlong(b_h);
                 const u64 t = (L >> 32) + H;
-                s[k + 6] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+                s[k + 6] = red96((u32)L, (u32)t, (u32)(t >> 32));
             }
         };
         emit(KTag<0>()); emit(KTag<1>()); emit(KTag<2>()); emit(KTag<3>()); emit(KTag<4>()); emit(KTag<5>());
@@ -357,7 +375,7 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
         dh = fma((double)mds_entry(0, i), dhi, dh);
         const u64 L = (u64)__double_as_longlong(dl), H = (u64)__double_as_longlong(dh); // raw: bias included
         const u64 t = (L >> 32) + H; // < 2^64
-        s[i] = gl::reduce96((u32)L, (u32)t, (u32)(t >> 32));
+        s[i] = red96((u32)L, (u32)t, (u32)(t >> 32));
     }
 #endif
 }
