@@ -253,7 +253,9 @@ def main():
     # instructions issued per clock per SM sub-partition with the fmaheavy (IMAD) pipe 63 % and the FP64 pipe 35 % busy -- the two
     # do not overlap in this instruction mix, their busy fractions add up to ~1; DRAM traffic 1.003x the algorithmic bytes
     # (4.376 GB moved for 4.362 GB on the 2^21 x 256 capture; a c2 launch is too long to replay)
-    INSTR_PER_PERM, TRAFFIC_RATIO, NCU_IPC, NCU_FMAHEAVY, NCU_FP64 = 13833.0, 1.003, 0.59, 0.630, 0.345
+    # The second CRT level on the cyclic half (adopted after that capture, profiles/r1_26) removes 12 FP64 operations per layer x
+    # 18 layers = 216 instructions per permutation: 13,833 - 216 = 13,617 (static SASS of the kernel 3712 -> 3648).
+    INSTR_PER_PERM, TRAFFIC_RATIO, NCU_IPC, NCU_FMAHEAVY, NCU_FP64 = 13617.0, 1.003, 0.59, 0.630, 0.345
     ipc = leaf_perm / (phase["leaf_ms"] / 1e3) / 32 * INSTR_PER_PERM / (148 * 4 * sm_hz)
     # observed in three captures (r1_18, r1_22, r1_24): fmaheavy-busy + FP64-busy = 1.01, 1.01, 0.98 -- in this instruction mix the
     # two pipes take turns instead of overlapping, so the issue rate saturates where their SUM reaches 1
@@ -264,7 +266,7 @@ def main():
                 "traffic_source": "dram__bytes_read+write of the same kernel captured with ncu --set full on the 2^21 x 256 shape (profiles/r1_24_leaf_ncu_split_circulant.txt), scaled by bytes",
                 "peak_source": peak_src,
                 "note": "the kernel is bound by instruction issue across the integer and FP64 pipes, not HBM: %.3f G Poseidon permutations/s = "
-                        "%.2f warp instr/clk/SMSP (ncu: 13.83 k instr per permutation, fmaheavy pipe 63%% busy, FP64 pipe 35%% busy with the "
+                        "%.2f warp instr/clk/SMSP (ncu: 13.6 k instr per permutation, fmaheavy pipe 63%% busy, FP64 pipe 35%% busy with the "
                         "exact-integer MDS layers, and the two busy fractions add up: the pipes alternate); that mix saturates at %.2f instr/clk/SMSP" % (leaf_perm / phase["leaf_ms"] / 1e6, ipc, cap),
                 "issue": {"warp_instr_per_clk_per_smsp": ipc, "model_cap": cap, "frac_of_model": ipc / cap}}
     epasses = (n * (1 if logn <= 8 else (logn + 7) // 8) + e * (1 if loge <= 8 else (loge + 7) // 8)) * ncols
