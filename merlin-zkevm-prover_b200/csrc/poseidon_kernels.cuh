@@ -121,6 +121,20 @@ __global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_linear_hash_ro
 {
     u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nrows) return;
+#ifdef GLB_LEAF_STAGGER
+    // Round-2 experiment (off by default): every row costs the same, so the CTAs of one SM start together and their warps move
+    // through the FP64 (MDS) and integer (S-box) stretches of the permutation in step.  Delay the first wave's CTA slots by
+    // GLB_LEAF_STAGGER clocks each so that the four warps of a sub-partition sit in different stretches
+    // (profiles/r1_27_ubench_fp64_phase.txt: -6 % on a synthetic two-phase loop); later CTAs inherit the offset of the slot they refill.
+    {
+        u32 nsm;
+        asm("mov.u32 %0, %%nsmid;" : "=r"(nsm));
+        if (blockIdx.x < GLB_LEAF_MINBLOCKS * nsm) {
+            const long long wait = (long long)((blockIdx.x / nsm) % GLB_LEAF_MINBLOCKS) * (GLB_LEAF_STAGGER), t0 = clock64();
+            while (clock64() - t0 < wait) { }
+        }
+    }
+#endif
     linear_hash_row<PANELS>(digests + row * 4, rp, PANELS ? nullptr : rp.base[0] + row * ncols, row, ncols);
 }
 
