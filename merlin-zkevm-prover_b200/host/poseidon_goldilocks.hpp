@@ -47,6 +47,50 @@ public:
         glb200::check(gl_linear_hash_host((uint64_t *)output, (const uint64_t *)input, size), "PoseidonGoldilocks::linear_hash");
     }
     static void linear_hash_seq(Goldilocks::Element *output, Goldilocks::Element *input, uint64_t size) { linear_hash(output, input, size); }
+
+    // merkletree_batch family (poseidon_goldilocks.hpp:44,51,60,68; .cpp:113-164,302-352,521-577): rows hashed in slices of
+    // batch_size columns, slice digests hashed again.  Not called by Starks / MerkleTreeGL; kept for the reference's tests.
+    static void merkletree_batch(Goldilocks::Element *tree, Goldilocks::Element *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size, int nThreads = 0, uint64_t dim = 1)
+    {
+        (void)nThreads;
+        if (num_rows == 0)
+            return;
+        glb200::check(gl_merkletree_batch_host((uint64_t *)tree, (const uint64_t *)input, num_cols * dim, num_rows, batch_size * dim), "PoseidonGoldilocks::merkletree_batch");
+    }
+    static void merkletree_batch_seq(Goldilocks::Element *tree, Goldilocks::Element *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size, int nThreads = 0, uint64_t dim = 1) { merkletree_batch(tree, input, num_cols, num_rows, batch_size, nThreads, dim); }
+    static void merkletree_batch_avx(Goldilocks::Element *tree, Goldilocks::Element *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size, int nThreads = 0, uint64_t dim = 1) { merkletree_batch(tree, input, num_cols, num_rows, batch_size, nThreads, dim); }
+    static void merkletree_batch_avx512(Goldilocks::Element *tree, Goldilocks::Element *input, uint64_t num_cols, uint64_t num_rows, uint64_t batch_size, int nThreads = 0, uint64_t dim = 1) { merkletree_batch(tree, input, num_cols, num_rows, batch_size, nThreads, dim); }
+
+    // The AVX-512 entry points work on TWO states / rows at once (poseidon_goldilocks.cpp:355-483).  Layout of the 24-word
+    // buffer: 4-word groups alternate between state A and state B -- word w of A at 8*(w/4) + w%4, of B at 8*(w/4) + 4 + w%4
+    // (see how linear_hash_avx512 fills it, :457-468).
+    static void hash_full_result_avx512(Goldilocks::Element *state, const Goldilocks::Element *input)
+    {
+        Goldilocks::Element two[2 * SPONGE_WIDTH];
+        for (int w = 0; w < SPONGE_WIDTH; w++)
+        {
+            two[w] = input[8 * (w / 4) + w % 4];
+            two[SPONGE_WIDTH + w] = input[8 * (w / 4) + 4 + w % 4];
+        }
+        glb200::check(gl_hash_full_result_host((uint64_t *)two, (const uint64_t *)two, 2), "PoseidonGoldilocks::hash_full_result_avx512");
+        for (int w = 0; w < SPONGE_WIDTH; w++)
+        {
+            state[8 * (w / 4) + w % 4] = two[w];
+            state[8 * (w / 4) + 4 + w % 4] = two[SPONGE_WIDTH + w];
+        }
+    }
+    static void hash_avx512(Goldilocks::Element (&state)[2 * CAPACITY], const Goldilocks::Element (&input)[2 * SPONGE_WIDTH])
+    {
+        Goldilocks::Element aux[2 * SPONGE_WIDTH];
+        hash_full_result_avx512(aux, input);
+        std::memcpy(state, aux, 2 * CAPACITY * sizeof(Goldilocks::Element)); // digest A | digest B
+    }
+    // input = row A (size words) followed by row B; output = digest A | digest B
+    static void linear_hash_avx512(Goldilocks::Element *output, Goldilocks::Element *input, uint64_t size)
+    {
+        linear_hash(output, input, size);
+        linear_hash(output + CAPACITY, input + size, size);
+    }
 };
 
 #endif

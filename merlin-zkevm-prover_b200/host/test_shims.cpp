@@ -134,6 +134,37 @@ static void test_concurrent_callers()
     for (int t = 0; t < nthreads; t++) EXPECT_EQ((uint64_t)bad[t], 0);
 }
 
+// merkletree_batch KAT (tests.cpp:2021-2052) and the two-state AVX-512 entry points against the one-state ones.
+static void test_batch_and_avx512_entry_points()
+{
+    uint64_t ncols = 128, nrows = 1 << 6;
+    std::vector<Goldilocks::Element> cols(ncols * nrows);
+    for (uint64_t i = 0; i < ncols; i++) cols[i] = cols[i + ncols] = Goldilocks::fromU64(i + 1);
+    for (uint64_t j = 2; j < nrows; j++)
+        for (uint64_t i = 0; i < ncols; i++) cols[j * ncols + i] = addm(cols[(j - 2) * ncols + i], cols[(j - 1) * ncols + i]);
+    std::vector<Goldilocks::Element> tree((2 * nrows - 1) * 4);
+    PoseidonGoldilocks::merkletree_batch_avx(tree.data(), cols.data(), ncols, nrows, 32);
+    EXPECT_EQ(Goldilocks::toU64(tree[tree.size() - 4]), 0XB2597514367E69FD);
+    EXPECT_EQ(Goldilocks::toU64(tree[tree.size() - 1]), 0X3E8670A179011526);
+
+    Goldilocks::Element a[12], b[12], ra[12], rb[12], two[24], out[24];
+    for (int w = 0; w < 12; w++) { a[w] = Goldilocks::fromU64(w * 3 + 1); b[w] = Goldilocks::fromU64(1000003ULL * (w + 7)); }
+    for (int w = 0; w < 12; w++) { two[8 * (w / 4) + w % 4] = a[w]; two[8 * (w / 4) + 4 + w % 4] = b[w]; }
+    PoseidonGoldilocks::hash_full_result(ra, a);
+    PoseidonGoldilocks::hash_full_result(rb, b);
+    PoseidonGoldilocks::hash_full_result_avx512(out, two);
+    for (int w = 0; w < 12; w++)
+    {
+        EXPECT_EQ(Goldilocks::toU64(out[8 * (w / 4) + w % 4]), Goldilocks::toU64(ra[w]));
+        EXPECT_EQ(Goldilocks::toU64(out[8 * (w / 4) + 4 + w % 4]), Goldilocks::toU64(rb[w]));
+    }
+    Goldilocks::Element d2[8], da[4], db[4];
+    PoseidonGoldilocks::linear_hash_avx512(d2, cols.data(), ncols); // rows 0 and 1
+    PoseidonGoldilocks::linear_hash(da, cols.data(), ncols);
+    PoseidonGoldilocks::linear_hash(db, cols.data() + ncols, ncols);
+    for (int k = 0; k < 4; k++) { EXPECT_EQ(Goldilocks::toU64(d2[k]), Goldilocks::toU64(da[k])); EXPECT_EQ(Goldilocks::toU64(d2[4 + k]), Goldilocks::toU64(db[k])); }
+}
+
 int main()
 {
     try
@@ -142,6 +173,7 @@ int main()
         test_ntt_roundtrip();
         test_extendPol_and_stage_commit();
         test_concurrent_callers();
+        test_batch_and_avx512_entry_points();
     }
     catch (const std::exception &e)
     {
