@@ -52,6 +52,24 @@ public:
     }
     ~NTT_Goldilocks() {}
 
+    // ntt_goldilocks.hpp:169-172: w(domainPow)^idx, i.e. roots[idx << (s - domainPow)] of the table the reference builds in its
+    // constructor.  No table is kept here (the transforms use the device table), so the value is computed on demand:
+    // w(k) = W[32]^(2^(32-k)) with W[32] = 7277203076849721926 (goldilocks_base_field.cpp:44).  The reference returned refers
+    // to a per-thread slot that the next call on the same thread overwrites.
+    Goldilocks::Element &root(u_int32_t domainPow, u_int64_t idx)
+    {
+        static thread_local Goldilocks::Element slot;
+        const uint64_t p = 0xFFFFFFFF00000001ULL;
+        auto mulm = [p](uint64_t a, uint64_t b) { return (uint64_t)(((unsigned __int128)a * b) % p); };
+        uint64_t w = 7277203076849721926ULL;
+        for (u_int32_t i = domainPow; i < 32; i++) w = mulm(w, w);
+        uint64_t r = 1;
+        for (uint64_t e = idx; e; e >>= 1, w = mulm(w, w))
+            if (e & 1) r = mulm(r, w);
+        slot = Goldilocks::fromU64(r);
+        return slot;
+    }
+
     void NTT(Goldilocks::Element *dst, Goldilocks::Element *src, u_int64_t size, u_int64_t ncols = 1, Goldilocks::Element *buffer = NULL, u_int64_t nphase = NUM_PHASES, u_int64_t nblock = NUM_BLOCKS, bool inverse = false, bool extend = false)
     {
         (void)buffer; (void)nphase; (void)nblock;

@@ -67,6 +67,12 @@ static void test_ntt_roundtrip()
     for (uint64_t i = 0; i < n * ncols; i++) EXPECT_EQ(Goldilocks::toU64(b[i]), Goldilocks::toU64(init[i]));
     gntt.NTT(a.data(), a.data(), 0, ncols);             // size 0 / ncols 0: no-op
     gntt.NTT(a.data(), a.data(), n, 0);
+    // root(domainPow, idx) = w(domainPow)^idx: w(1) = -1, w(4) = 2^12, w(6) = 2^3 (goldilocks_base_field.cpp:11-18)
+    EXPECT_EQ(Goldilocks::toU64(gntt.root(1, 1)), P - 1);
+    EXPECT_EQ(Goldilocks::toU64(gntt.root(4, 1)), 1ULL << 12);
+    EXPECT_EQ(Goldilocks::toU64(gntt.root(6, 5)), 1ULL << 15);
+    EXPECT_EQ(Goldilocks::toU64(gntt.root(4, 16)), 1);
+    EXPECT_EQ(Goldilocks::toU64(gntt.root(32, 1)), 7277203076849721926ULL);
     bool thrown = false;
     try { NTT_Goldilocks big((uint64_t)1 << 33); } catch (const std::range_error &) { thrown = true; }
     EXPECT_EQ(thrown ? 1 : 0, 1);
