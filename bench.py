@@ -15,9 +15,8 @@ extended domain) of every column followed by MerkleTreeGL::merkelize of the exte
              when the reference was not compiled -- timed on a bounded sample of the same workload
 
 `--impl reference` times only that CPU arm, with the same JSON schema.
-Under torchrun (N>1) the workload is column-split over ranks for the LDE, exchanged to row blocks and
-each rank hashes its rows (weak scaling: every rank carries a full `workload` worth of columns/N ... see
-DESIGN.md "Multi-GPU").
+Under torchrun (N>1) the SAME workload is column-split over ranks for the LDE, exchanged to row blocks and
+each rank hashes its rows (strong scaling: total work fixed, see DESIGN.md "Multi-GPU").
 """
 import argparse
 import json
@@ -43,6 +42,8 @@ WORKLOADS = {
     "mid": (20, 21, 256),    # profiling shape: row pitch 2 KiB, fits ncu kernel replay
 }
 SEED = 1
+# ncu capture of the shipped leaf kernel (per-opcode warp-instruction counts from the source page)
+INSTR_PER_PERM, TRAFFIC_RATIO, INSTR_SOURCE = 13617.0, 1.003, "profiles/r1_24_leaf_ncu_split_circulant.txt minus 216 (static SASS delta of the second CRT level)"
 
 
 def peaks():
@@ -109,53 +110,85 @@ def permutations(loge, ncols):
 
 
 # --------------------------------------------------------------------------------------- CPU arm
-def cpu_arm(logn, loge, ncols, budget_s, steps, warmup):
-    """Reference CPU implementation on a bounded sample: same rows, fewer columns, all host threads."""
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_arm(logn, loge, ncols, budget_s, steps, warmup, total_budget_s=None):
+    """The reference's own CPU implementation (oracle/_ref; the oracle port when it was never built) on a bounded sample of
+    the workload: the SAME rows and the first `cols` of the `ncols` columns of the same synthetic matrix, all host threads.
+    The LDE cost is per column and the hashing cost per permutation, so the full-width figure is
+        t(C) = C * t_lde_per_col + perms(E, C) / perm_rate,    perms(E, C) = E * ceil(C / 8) + E - 1,
+    with both rates measured on the sample (a narrow sample alone overstates the per-element hashing cost: at 8 columns
+    a row costs 2 permutations per 8 elements, at 600 columns 76 per 600).  Returns (dict, sampled LDE columns)."""
     from oracle import pyoracle
     r = pyoracle.ref(prefer_avx512=True)  # fastest build the host supports (AVX-512 Poseidon if avx512f, else the default AVX2)
     kind = "reference" if r is not None else "port"
     o = pyoracle.oracle()
+    nthreads = host_threads()
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: set the team size explicitly
+    if r is not None:
+        r.L.ref_set_num_threads(nthreads)
+    o.L.glo_set_num_threads(nthreads)
     cores = (r.L.ref_num_threads() if r is not None else o.L.glo_num_threads())
     n, e = 1 << logn, 1 << loge
     import __graft_entry__ as ge
     glb = ge.load()
 
+    def perms(c):
+        return (e * ((c + 7) // 8) if c > 4 else 0) + e - 1
+
     def run(cols):
-        x = glb.synthetic_host(n * cols, SEED).reshape(n, cols)
+        x = np.ascontiguousarray(glb.synthetic_host_cols(n, ncols, np.arange(cols), SEED))
         t0 = time.perf_counter()
         if r is not None:
             lde, tree, ms_lde, ms_tree = r.commit(x, e)
-            root = r.canon(tree[-4:])
+            lde = r.canon(lde)
         else:
+            t1 = time.perf_counter()
             lde = o.extend_pol(x, e)
+            t2 = time.perf_counter()
             tree = o.merkletree(lde)
-            root = tree[-4:]
-            ms_lde = ms_tree = None
+            ms_lde, ms_tree = (t2 - t1) * 1e3, (time.perf_counter() - t2) * 1e3
         dt = time.perf_counter() - t0
-        return dt, root, ms_lde, ms_tree
+        return dt, lde, ms_lde, ms_tree
 
-    # calibrate on 8 columns, then size the sample to the per-step budget (perm count per element kept close
-    # to the full workload's by preferring multiples of 8 columns)
-    dt8, _, _, _ = run(8)
+    # calibrate on 8 columns, then size the sample: a multiple of 8 columns, >= 32 when the budget allows, within the per-step
+    # and the whole-run budget
+    t_start = time.perf_counter()
+    dt8, lde, a8, b8 = run(8)
     per_col = dt8 / 8.0
-    cols = int(max(8, min(ncols, (budget_s / per_col) // 8 * 8)))
-    times = []
-    detail = None
-    for i in range(warmup + steps):
-        dt, root, a, b = run(cols)
-        if i >= warmup:
-            times.append(dt)
-            detail = (a, b)
-    best = float(np.mean(times)) if times else dt8
-    if not times:
-        cols = 8
+    if total_budget_s is not None:
+        budget_s = min(budget_s, max(dt8, (total_budget_s - dt8) / max(1, steps + warmup)))
+    cols = int(max(8, min(ncols // 8 * 8 if ncols >= 8 else 8, (budget_s / per_col) // 8 * 8)))
+    ms_lde, ms_tree, times = [a8], [b8], []
+    if cols > 8 or steps + warmup > 0:
+        ms_lde, ms_tree = [], []
+        for i in range(warmup + steps):
+            if total_budget_s is not None and i > 0 and time.perf_counter() - t_start + per_col * cols > total_budget_s:
+                break                                    # never run into the driver's timeout
+            dt, lde, a, b = run(cols)
+            if i >= warmup or i == warmup + steps - 1:
+                times.append(dt)
+                ms_lde.append(a)
+                ms_tree.append(b)
+        if not times:
+            cols, ms_lde, ms_tree = 8, [a8], [b8]
+    t_lde_col = float(np.mean(ms_lde)) / 1e3 / cols
+    perm_rate = perms(cols) / (float(np.mean(ms_tree)) / 1e3)
+    t_full = ncols * t_lde_col + perms(ncols) / perm_rate
     return {
-        "value": e * cols / best, "unit": "ext-elem/s", "cores": int(cores), "kind": kind,
-        "sample": "2^%d rows x %d of %d columns -> 2^%d (same rows, column-reduced; LDE is column-independent, leaf hash cost is per 8 columns); extendPol + merkletree_%s, %d timed runs, mean %.2f s%s"
-                  % (logn, cols, ncols, loge, ("avx512" if (r is not None and r.avx512) else "avx"), len(times), best,
-                     "" if detail is None or detail[0] is None else " (LDE %.0f ms, tree %.0f ms)" % detail),
-        "ms_per_step_sample": best * 1e3,
-    }, best
+        "value": e * ncols / t_full, "unit": "ext-elem/s", "cores": int(cores), "kind": kind,
+        "sample": "2^%d rows x the first %d of %d columns -> 2^%d, extendPol + merkletree_%s on %d threads, %d timed runs: LDE %.1f ms (%.2f ms per column), "
+                  "hashing %.1f ms (%.3g permutations/s); projected to %d columns as C*t_lde_per_col + (E*ceil(C/8)+E-1)/perm_rate = %.1f s"
+                  % (logn, cols, ncols, loge, ("avx512" if (r is not None and r.avx512) else ("avx" if r is not None else "oracle-port")), cores, max(1, len(times)),
+                     float(np.mean(ms_lde)), t_lde_col * 1e3, float(np.mean(ms_tree)), perm_rate, ncols, t_full),
+        "ncols_sampled": cols, "ms_per_step_projected": t_full * 1e3, "ms_per_step_sample": (float(np.mean(ms_lde)) + float(np.mean(ms_tree))),
+        "sample_ext_elem_per_s": e * cols / ((float(np.mean(ms_lde)) + float(np.mean(ms_tree))) / 1e3),
+    }, lde
 
 
 def main():
@@ -185,11 +218,14 @@ def main():
             return 0
         total = max(1, args.steps + args.warmup)
         budget = args.cpu_budget if args.cpu_budget else max(2.0, min(25.0, 150.0 / total))
-        cb, sec = cpu_arm(logn, loge, ncols, budget, args.steps, args.warmup)
+        cb, _ = cpu_arm(logn, loge, ncols, budget, args.steps, args.warmup, total_budget_s=170.0)
+        config = dict(config, ncols_sampled=cb["ncols_sampled"],
+                      sampling="CPU arm runs the first ncols_sampled columns of the same rows; value is projected to ncols (formula in cpu_baseline.sample)")
         line = {"impl": "reference", "metric": "commit_ext_elements_per_s", "value": cb["value"], "unit": "ext-elem/s", "n_gpus": args.gpus,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step_sample"], "higher_is_better": True,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step_projected"], "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "u64 (Goldilocks field)", "data": "synthetic", "config": config,
                 "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "sample_ext_elem_per_s": cb["sample_ext_elem_per_s"], "ms_per_step_sample": cb["ms_per_step_sample"],
                 "e2e": {"value": cb["value"], "unit": "ext-elem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
         print(json.dumps(line))
         return 0
@@ -243,41 +279,50 @@ def main():
         phase[k] /= args.steps
     value = e * ncols / (dev_ms / 1e3)
 
-    # ---- roofline
+    # ---- roofline of the dominant kernel (leaf hashing).  It is bound by instruction issue on the integer/FP64 pipes, not by HBM
+    # (SURVEY 8d), so the fraction is against issue rates MEASURED NOW on this device by gl_measure_issue_peaks (real IMAD.WIDE.U32,
+    # IADD3 and DFMA chains; SASS checked in tools/ubench_pipes.cu), and the HBM figure is kept as a secondary entry.
     leaf_perm, tree_perm = permutations(loge, ncols)
     leaf_bytes = e * ncols * 8 + e * 32                 # read the extended matrix once, write the digests
     lde_bytes, lde_passes = lde_pass_bytes(logn, loge, ncols)
-    sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
-    # ncu (profiles/r1_24_leaf_ncu_split_circulant.txt): 13,833 warp instructions per permutation in k_linear_hash_rows (4,082 of
-    # them DFMA/DADD/DMUL: the split-circulant MDS layers, one per full round and one per PAIR of partial rounds); 0.59
-    # instructions issued per clock per SM sub-partition with the fmaheavy (IMAD) pipe 63 % and the FP64 pipe 35 % busy -- the two
-    # do not overlap in this instruction mix, their busy fractions add up to ~1; DRAM traffic 1.003x the algorithmic bytes
-    # (4.376 GB moved for 4.362 GB on the 2^21 x 256 capture; a c2 launch is too long to replay)
-    # The second CRT level on the cyclic half (adopted after that capture, profiles/r1_26) removes 12 FP64 operations per layer x
-    # 18 layers = 216 instructions per permutation: 13,833 - 216 = 13,617 (static SASS of the kernel 3712 -> 3648).
-    INSTR_PER_PERM, TRAFFIC_RATIO, NCU_IPC, NCU_FMAHEAVY, NCU_FP64 = 13617.0, 1.003, 0.59, 0.630, 0.345
-    ipc = leaf_perm / (phase["leaf_ms"] / 1e3) / 32 * INSTR_PER_PERM / (148 * 4 * sm_hz)
-    # observed in three captures (r1_18, r1_22, r1_24): fmaheavy-busy + FP64-busy = 1.01, 1.01, 0.98 -- in this instruction mix the
-    # two pipes take turns instead of overlapping, so the issue rate saturates where their SUM reaches 1
-    cap = min(1.0, NCU_IPC / (NCU_FMAHEAVY + NCU_FP64))
+    pk = glb.measure_issue_peaks()
+    perm_rate = leaf_perm / (phase["leaf_ms"] / 1e3)
+    # warp instructions per permutation of the shipped k_linear_hash_rows: ncu source page, see INSTR_SOURCE
+    warp_instr_rate = perm_rate / 32 * INSTR_PER_PERM
+    issue_peak = pk["iadd3_lane_ops_per_s"] / 32        # one warp instruction per clock per SM sub-partition, measured
+    # SURVEY 8(d) accounting of the REFERENCE algorithm: 1144 modular multiplications x 5 IMAD.WIDE-class + 1008 small-constant
+    # MACs x 2 per permutation; our dense / paired form needs fewer real multiplies, so this credits the algorithmic saving
+    imad_algo = perm_rate * (1144 * 5 + 1008 * 2)
     roofline = {"kernel": "poseidon::k_linear_hash_rows (leaf hashing, %.0f%% of the step)" % (100 * phase["leaf_ms"] / dev_ms),
-                "bound": "hbm", "achieved": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                "frac": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9 / hbm_peak, "traffic": leaf_bytes * TRAFFIC_RATIO,
-                "traffic_source": "dram__bytes_read+write of the same kernel captured with ncu --set full on the 2^21 x 256 shape (profiles/r1_24_leaf_ncu_split_circulant.txt), scaled by bytes",
-                "peak_source": peak_src,
-                "note": "the kernel is bound by instruction issue across the integer and FP64 pipes, not HBM: %.3f G Poseidon permutations/s = "
-                        "%.2f warp instr/clk/SMSP (ncu: 13.6 k instr per permutation, fmaheavy pipe 63%% busy, FP64 pipe 35%% busy with the "
-                        "exact-integer MDS layers, and the two busy fractions add up: the pipes alternate); that mix saturates at %.2f instr/clk/SMSP" % (leaf_perm / phase["leaf_ms"] / 1e6, ipc, cap),
-                "issue": {"warp_instr_per_clk_per_smsp": ipc, "model_cap": cap, "frac_of_model": ipc / cap}}
+                "bound": "issue", "achieved": warp_instr_rate / 1e12, "peak": issue_peak / 1e12, "unit": "T warp-instr/s",
+                "frac": warp_instr_rate / issue_peak,
+                "peak_source": "gl_measure_issue_peaks() in this run: IADD3 chain = %.3f T warp-instr/s (148 SMs x 4 sub-partitions x SM clock); "
+                               "IMAD.WIDE.U32 %.2f T lane-ops/s, DFMA %.2f T lane-ops/s" % (issue_peak / 1e12, pk["imad_wide_lane_ops_per_s"] / 1e12, pk["dfma_lane_ops_per_s"] / 1e12),
+                "instr_per_permutation": INSTR_PER_PERM, "instr_source": INSTR_SOURCE,
+                "Gperm_per_s": perm_rate / 1e9,
+                "imad": {"achieved_lane_ops_per_s": imad_algo, "peak_lane_ops_per_s": pk["imad_wide_lane_ops_per_s"], "frac": imad_algo / pk["imad_wide_lane_ops_per_s"],
+                         "note": "SURVEY 8(d) accounting of the reference algorithm (1144 modmul x 5 + 1008 MAC x 2 IMAD-class lane-ops per permutation) against the measured real "
+                                 "IMAD.WIDE.U32 rate; above 1 means the dense-form kernel executes fewer multiplies than that accounting assumes"},
+                "hbm": {"achieved": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9 / hbm_peak,
+                        "peak_source": peak_src},
+                "traffic": leaf_bytes * TRAFFIC_RATIO,
+                "traffic_source": "dram__bytes_read+write of the same kernel, ncu --set full on the 2^21 x 256 shape (%s), scaled by bytes" % INSTR_SOURCE}
     epasses = (n * (1 if logn <= 8 else (logn + 7) // 8) + e * (1 if loge <= 8 else (loge + 7) // 8)) * ncols
+    lde_algo = (n + e) * ncols * 8
     phases = {
-        "lde": {"ms": phase["lde_ms"], "kernels": "ntt::k_pass x %d passes per column block" % lde_passes, "bound": "integer issue, then hbm",
-                "algorithmic_bytes": lde_bytes, "achieved_GBps": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9,
+        "lde": {"ms": phase["lde_ms"], "kernels": "ntt::k_pass x %d passes per column block" % lde_passes, "bound": "hbm (per pass: one read + one write of the matrix)",
+                "pass_bytes": lde_bytes, "achieved_GBps": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9,
                 "frac": lde_bytes / (phase["lde_ms"] / 1e3) / 1e9 / hbm_peak, "element_passes": epasses,
-                "ns_per_element_pass": phase["lde_ms"] * 1e6 / epasses},
+                "ns_per_element_pass": phase["lde_ms"] * 1e6 / epasses,
+                "algorithmic_bytes": lde_algo, "algorithmic_frac": lde_algo / (phase["lde_ms"] / 1e3) / 1e9 / hbm_peak},
         "leaf": {"ms": phase["leaf_ms"], "permutations": leaf_perm, "Gperm_per_s": leaf_perm / phase["leaf_ms"] / 1e6},
         "tree": {"ms": phase["tree_ms"], "permutations": tree_perm, "Gperm_per_s": tree_perm / max(phase["tree_ms"], 1e-9) / 1e6},
     }
+
+    # the first columns of the GPU's LDE, kept for the parity check against the CPU arm below
+    lde_head = None
+    if not args.no_cpu:
+        lde_head = glb.download_cols(dlde.ptr, e, ncols, 0, min(32, ncols))
 
     # ---- end to end through the host-pointer C ABI (pinned host buffers)
     e2e = None
@@ -319,12 +364,20 @@ def main():
                 if hp.value:
                     L.gl_host_free(hp)
 
-    # ---- CPU baseline on a bounded sample
+    # ---- CPU baseline on a bounded sample, and the parity check of the sample against the GPU's LDE of the same columns
     cpu = None
+    parity = {"parity_checked": False}
     if not args.no_cpu:
         try:
-            cb, _ = cpu_arm(logn, loge, ncols, args.cpu_budget or 12.0, 1, 0)
+            cb, lde_cpu = cpu_arm(logn, loge, ncols, args.cpu_budget or 12.0, 1, 0)
             cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            k = min(lde_cpu.shape[1], lde_head.shape[1])
+            same = bool(np.array_equal(lde_cpu[:, :k], lde_head[:, :k]))
+            parity = {"parity_checked": same, "parity": "every word of the first %d LDE columns (2^%d rows) equals the CPU %s's extendPol of the same input columns: %s"
+                      % (k, loge, cb["kind"], same)}
+            assert same, "GPU LDE differs from the CPU reference on the sampled columns"
+        except AssertionError:
+            raise
         except Exception as ex:
             cpu = {"value": None, "unit": "ext-elem/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %s" % str(ex)[:160]}
 
@@ -333,6 +386,7 @@ def main():
             "dtype": "u64 (Goldilocks field, integer pipe)", "data": "synthetic (splitmix64 of the element index mod p, generated in HBM)",
             "config": config, "root": " ".join("%016X" % int(v) for v in root), "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "phases": phases, "cpu_baseline": cpu}
+    line.update(parity)
     print(json.dumps(line))
     return 0
 

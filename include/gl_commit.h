@@ -44,7 +44,7 @@ int gl_init(int device);
 void gl_shutdown(void);
 const char *gl_last_error(void);
 int gl_device_count(int *count);
-/* Upper bound (bytes) for the library's internal scratch arena; 0 = default (4 GiB). */
+/* Upper bound (bytes) for the library's internal scratch arena; 0 = default (8 GiB). */
 int gl_set_scratch_limit(size_t bytes);
 /* Number of CUDA kernels launched by this library since the last call with reset != 0. */
 uint64_t gl_kernel_launches(int reset);
@@ -61,6 +61,9 @@ int gl_host_unregister(void *hptr);
 int gl_h2d(void *dptr, const void *hptr, size_t bytes);
 int gl_d2h(void *hptr, const void *dptr, size_t bytes);
 int gl_sync(void);
+/* Strided copy (cudaMemcpy2D semantics, pitches and width in bytes): kind 0 host->device, 1 device->host,
+ * 2 device->device.  Used to move column blocks of row-major matrices (NTT nblock > 1, ntt_goldilocks.cpp:199-227). */
+int gl_copy2d(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width_bytes, size_t rows, int kind);
 /* cudaStream_t of the library (as void*), for callers that want to order their own work. */
 void *gl_stream(void);
 
@@ -89,6 +92,14 @@ int gl_commit_dev(uint64_t *lde, uint64_t *tree, const uint64_t *in, uint64_t n_
  * = row idx of src followed by the sibling digests bottom-up; src/tree are device pointers. */
 int gl_group_proof_dev(uint64_t *proof_host, const uint64_t *src, const uint64_t *tree,
                        uint64_t height, uint64_t width, uint64_t idx);
+/* All queries of one tree in ONE launch and ONE download (FRIProve::queryPol loop, friProve.cpp:219-250, over
+ * MerkleTreeGL::getGroupProof, merkleTreeGL.cpp:12-35): proofs_host receives n proofs of width + 4*log2(height) words
+ * back to back; idx_host holds the n row indices (HOST).  No device allocation on the steady-state path. */
+int gl_group_proofs_dev(uint64_t *proofs_host, const uint64_t *src, const uint64_t *tree, uint64_t height,
+                        uint64_t width, const uint64_t *idx_host, uint64_t n);
+/* n rows of a device-resident row-major matrix (the LDE row reads of Starks::evmap, starks.cpp:555-668):
+ * rows_host[q*width + j] = src[idx_host[q]*width + j], canonical. */
+int gl_rows_gather_dev(uint64_t *rows_host, const uint64_t *src, uint64_t width, const uint64_t *idx_host, uint64_t n);
 /* Batched permutation PoseidonGoldilocks::hash_full_result (poseidon_goldilocks.cpp:166-228):
  * n states of 12 words. */
 int gl_hash_full_result_dev(uint64_t *out, const uint64_t *in, uint64_t n);
@@ -113,6 +124,10 @@ int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const 
 /* Benchmark helper (not on the commit path): dst[i] = splitmix64(seed + (first_index+i)*0x9E3779B97F4A7C15)
  * mod p, i < words; dst is a device pointer. */
 int gl_fill_synthetic_dev(uint64_t *dst, uint64_t words, uint64_t seed, uint64_t first_index);
+
+/* Measurement helper for bench.py's roofline (not on the commit path): issue rates measured now on this device, in
+ * lane-operations per second: [0] IMAD.WIDE.U32 (32x32+64), [1] IADD3, [2] DFMA. */
+int gl_measure_issue_peaks(double lane_ops_per_s[3]);
 
 /* ---- layout helpers (merklehash_goldilocks.hpp:25-28, merkleTreeGL.hpp:71-78) ----------------- */
 uint64_t gl_tree_num_elements(uint64_t height);

@@ -50,6 +50,10 @@ SIGNATURES = {
     "gl_merkletree_batch_host": (C.c_int, [_u64p, _u64p, _u64, _u64, _u64]),
     "gl_commit_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64p]),
     "gl_group_proof_dev": (C.c_int, [_u64p, C.c_void_p, C.c_void_p, _u64, _u64, _u64]),
+    "gl_group_proofs_dev": (C.c_int, [_u64p, C.c_void_p, C.c_void_p, _u64, _u64, _u64p, _u64]),
+    "gl_rows_gather_dev": (C.c_int, [_u64p, C.c_void_p, _u64, _u64p, _u64]),
+    "gl_copy2d": (C.c_int, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]),
+    "gl_measure_issue_peaks": (C.c_int, [C.POINTER(C.c_double)]),
     "gl_hash_full_result_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64]),
     "gl_linear_hash_rows_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64]),
     "gl_ntt_host": (C.c_int, [_u64p, _u64p, _u64, _u64, C.c_int, C.c_int]),
@@ -219,6 +223,46 @@ def group_proof_dev(src, tree, height, width, idx):
     proof = np.zeros(proof_size(height, width), dtype=np.uint64)
     _check(lib().gl_group_proof_dev(_p(proof), C.c_void_p(src), C.c_void_p(tree), height, width, idx))
     return proof
+
+
+def group_proofs_dev(src, tree, height, width, idxs):
+    """All queries of one tree in one launch (FRIProve::queryPol, friProve.cpp:219-250)."""
+    idxs = np.ascontiguousarray(idxs, dtype=np.uint64)
+    proofs = np.zeros((idxs.size, proof_size(height, width)), dtype=np.uint64)
+    _check(lib().gl_group_proofs_dev(_p(proofs), C.c_void_p(src), C.c_void_p(tree), height, width, _p(idxs), idxs.size))
+    return proofs
+
+
+def rows_gather_dev(src, width, idxs):
+    idxs = np.ascontiguousarray(idxs, dtype=np.uint64)
+    rows = np.zeros((idxs.size, width), dtype=np.uint64)
+    _check(lib().gl_rows_gather_dev(_p(rows), C.c_void_p(src), width, _p(idxs), idxs.size))
+    return rows
+
+
+def download_cols(dptr, nrows, pitch, c0, w):
+    """Columns [c0, c0+w) of a device-resident row-major nrows x pitch matrix as a packed (nrows, w) host array."""
+    out = np.empty((nrows, w), dtype=np.uint64)
+    _check(lib().gl_copy2d(out.ctypes.data_as(C.c_void_p), w * 8, C.c_void_p(dptr + 8 * c0), pitch * 8, w * 8, nrows, 1))
+    return out
+
+
+def measure_issue_peaks():
+    v = (C.c_double * 3)()
+    _check(lib().gl_measure_issue_peaks(v))
+    return {"imad_wide_lane_ops_per_s": v[0], "iadd3_lane_ops_per_s": v[1], "dfma_lane_ops_per_s": v[2]}
+
+
+def synthetic_host_cols(nrows, ncols_total, cols, seed=1):
+    """Columns `cols` (array of column indices) of the nrows x ncols_total matrix gl_fill_synthetic_dev generates."""
+    cols = np.asarray(cols, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        i = (np.arange(nrows, dtype=np.uint64)[:, None] * np.uint64(ncols_total) + cols[None, :])
+        z = np.uint64(seed) + i * np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return np.where(z >= np.uint64(P), z - np.uint64(P), z)
 
 
 # ---- host-pointer calls (what the C++ shims use) -----------------------------------------------

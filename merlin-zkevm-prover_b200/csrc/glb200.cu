@@ -68,6 +68,8 @@ struct Ctx {
     size_t scratch_limit = (size_t)8 << 30;
     std::atomic<uint64_t> launches{0};
     float ms[4] = {0, 0, 0, 0}; // LDE, leaf hashing, tree levels, multi-GPU exchange
+    u64 *qbuf = nullptr;        // grow-only staging of the batched query calls: [indices | gathered words] (device)
+    size_t qbuf_words = 0;
     std::mutex mu;
 } g;
 
@@ -399,6 +401,64 @@ __global__ void k_gather_proof(u64 *proof, const u64 *src, const u64 *tree, u64 
     proof[tid] = gl::canon(tree[off + sib * 4 + (k & 3)]);
 }
 
+// n proofs in one launch: blockIdx.y = query, proof q at proofs + q * words (MerkleTreeGL::getGroupProof for every query of
+// one tree, friProve.cpp:219-250).  An index >= height yields an all-zero proof (the host side rejects it beforehand).
+__global__ void k_gather_proofs(u64 *proofs, const u64 *src, const u64 *tree, u64 height, u64 width, u64 words, const u64 *idx_list)
+{
+    const u64 tid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= words) return;
+    const u64 idx = idx_list[blockIdx.y];
+    u64 *proof = proofs + (u64)blockIdx.y * words;
+    if (tid < width) {
+        proof[tid] = gl::canon(src[idx * width + tid]);
+        return;
+    }
+    const u64 k = tid - width, level = k >> 2;
+    u64 off = 0, n = height;
+    for (u64 l = 0; l < level; l++) {
+        off += n * 4;
+        n >>= 1;
+    }
+    proof[tid] = n > 1 ? gl::canon(tree[off + ((idx >> level) ^ 1) * 4 + (k & 3)]) : 0;
+}
+
+// n rows of a row-major matrix in one launch (the row reads of Starks::evmap, starks.cpp:555-668): out[q][.] = src[idx[q]][.]
+__global__ void k_gather_rows(u64 *out, const u64 *src, u64 width, const u64 *idx_list)
+{
+    const u64 tid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= width) return;
+    out[(u64)blockIdx.y * width + tid] = gl::canon(src[idx_list[blockIdx.y] * width + tid]);
+}
+
+// Issue-rate probes for bench.py's roofline (not on the commit path): one real IMAD.WIDE.U32 / IADD3 / DFMA per chain step, 8
+// independent chains per thread, the forms whose SASS tools/ubench_pipes.cu verifies (nothing is strength-reduced away).
+template <int OP>
+__global__ void __launch_bounds__(512) k_issue_probe(u64 *out, int iters, u32 seed)
+{
+    u32 a = seed + threadIdx.x, b = seed * 3 + blockIdx.x + threadIdx.x * 5;
+    u64 acc[8];
+    u32 r[8];
+    double d[8];
+    const double m = 1.0 + 1e-9 * seed, c = 1e-3 * threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < 8; i++) { acc[i] = ((u64)b << 32) + a + i; r[i] = a * (i + 1); d[i] = 1.0 + i; }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int rep = 0; rep < 8; rep++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                if (OP == 0) asm volatile("{ .reg .u32 lo, hi, x, y; mov.b64 {lo, hi}, %0; mov.b64 {x, y}, %1; mad.lo.cc.u32 x, lo, hi, x; madc.hi.u32 y, lo, hi, y; mov.b64 %0, {x, y}; }" : "+l"(acc[i]) : "l"(acc[(i + 1) & 7]));
+                if (OP == 1) asm volatile("{ .reg .u32 z; add.u32 z, %0, %1; add.u32 %0, z, %2; }" : "+r"(r[i]) : "r"(r[(i + 1) & 7]), "r"(r[(i + 2) & 7]));
+                if (OP == 2) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(d[i]) : "d"(m), "d"(c));
+            }
+        }
+    }
+    u64 x = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) x += acc[i] + r[i] + (u64)__double_as_longlong(d[i]);
+    out[(u64)blockIdx.x * blockDim.x + threadIdx.x] = x;
+}
+
 // Batched Goldilocks::add/sub/mul (goldilocks_base_field_scalar.hpp:16-160) -- F1 parity entry point.
 __global__ void k_field_op(u64 *out, const u64 *a, const u64 *b, const u64 *c, u64 n, int op)
 {
@@ -662,6 +722,9 @@ void gl_shutdown(void)
     g.arena_bytes = 0;
     if (g.roots) cudaFree(g.roots);
     if (g.rscale) cudaFree(g.rscale);
+    if (g.qbuf) cudaFree(g.qbuf);
+    g.qbuf = nullptr;
+    g.qbuf_words = 0;
     g.roots = g.rscale = nullptr;
     g.log_roots = g.log_rscale = 0;
     for (auto &e : g.ev) { cudaEventDestroy(e); e = nullptr; }
@@ -803,6 +866,101 @@ int gl_group_proof_dev(uint64_t *proof_host, const uint64_t *src, const uint64_t
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(proof_host, d.p, words * 8, cudaMemcpyDeviceToHost, g.stream));
     CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+// grow-only device staging for the batched query calls (no cudaMalloc on the steady-state path)
+static int qbuf_reserve(size_t words)
+{
+    if (words <= g.qbuf_words) return GL_OK;
+    if (g.qbuf) {
+        CU(cudaStreamSynchronize(g.stream));
+        CU(cudaFree(g.qbuf));
+        g.qbuf = nullptr;
+        g.qbuf_words = 0;
+    }
+    size_t cap = words < 4096 ? 4096 : words + words / 2;
+    CU(cudaMalloc(&g.qbuf, cap * 8));
+    g.qbuf_words = cap;
+    return GL_OK;
+}
+
+int gl_group_proofs_dev(uint64_t *proofs_host, const uint64_t *src, const uint64_t *tree, uint64_t height, uint64_t width,
+                        const uint64_t *idx_host, uint64_t n)
+{
+    API_ENTER();
+    if (n == 0) return GL_OK;
+    if (height == 0) return fail(GL_ERR_ARG, "getGroupProof: empty tree");
+    for (u64 q = 0; q < n; q++)
+        if (idx_host[q] >= height) return fail(GL_ERR_ARG, "getGroupProof: idx %llu out of range (query %llu)", (u64)idx_host[q], q);
+    if (n > 65535) return fail(GL_ERR_ARG, "getGroupProof: at most 65535 queries per call");
+    u64 levels = 0;
+    while ((height >> levels) > 1) levels++;
+    const u64 words = width + 4 * levels;
+    if (words == 0) return GL_OK;
+    TRY(qbuf_reserve(n + n * words));
+    u64 *didx = g.qbuf, *dproofs = g.qbuf + n;
+    CU(cudaMemcpyAsync(didx, idx_host, n * 8, cudaMemcpyHostToDevice, g.stream));
+    k_gather_proofs<<<dim3((unsigned)((words + 127) / 128), (unsigned)n), 128, 0, g.stream>>>(dproofs, (const u64 *)src, (const u64 *)tree, height, width,
+                                                                                             words, didx);
+    g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(proofs_host, dproofs, n * words * 8, cudaMemcpyDeviceToHost, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_rows_gather_dev(uint64_t *rows_host, const uint64_t *src, uint64_t width, const uint64_t *idx_host, uint64_t n)
+{
+    API_ENTER();
+    if (n == 0 || width == 0) return GL_OK;
+    if (n > 65535) return fail(GL_ERR_ARG, "rows_gather: at most 65535 rows per call");
+    TRY(qbuf_reserve(n + n * width));
+    u64 *didx = g.qbuf, *drows = g.qbuf + n;
+    CU(cudaMemcpyAsync(didx, idx_host, n * 8, cudaMemcpyHostToDevice, g.stream));
+    k_gather_rows<<<dim3((unsigned)((width + 127) / 128), (unsigned)n), 128, 0, g.stream>>>(drows, (const u64 *)src, width, didx);
+    g.launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(rows_host, drows, n * width * 8, cudaMemcpyDeviceToHost, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_copy2d(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width_bytes, size_t rows, int kind)
+{
+    API_ENTER();
+    if (width_bytes == 0 || rows == 0) return GL_OK;
+    if (kind < 0 || kind > 2) return fail(GL_ERR_ARG, "copy2d: kind %d (0 H2D, 1 D2H, 2 D2D)", kind);
+    const cudaMemcpyKind k = kind == 0 ? cudaMemcpyHostToDevice : (kind == 1 ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice);
+    CU(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width_bytes, rows, k, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_measure_issue_peaks(double lane_ops_per_s[3])
+{
+    API_ENTER();
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, g.device));
+    const int blocks = prop.multiProcessorCount * 2, threads = 512, iters = 2000;
+    DevBuf out;
+    TRY(out.alloc((size_t)blocks * threads * 8));
+    for (int op = 0; op < 3; op++) {
+        float best = 1e30f;
+        for (int rep = 0; rep < 3; rep++) {
+            CU(cudaEventRecord(g.ev[4], g.stream));
+            if (op == 0) k_issue_probe<0><<<blocks, threads, 0, g.stream>>>((u64 *)out.p, iters, 12345);
+            if (op == 1) k_issue_probe<1><<<blocks, threads, 0, g.stream>>>((u64 *)out.p, iters, 12345);
+            if (op == 2) k_issue_probe<2><<<blocks, threads, 0, g.stream>>>((u64 *)out.p, iters, 12345);
+            g.launches++;
+            CU(cudaEventRecord(g.ev[5], g.stream));
+            CU(cudaStreamSynchronize(g.stream));
+            float ms = 0;
+            CU(cudaEventElapsedTime(&ms, g.ev[4], g.ev[5]));
+            if (rep && ms < best) best = ms;
+        }
+        lane_ops_per_s[op] = (double)iters * 64.0 * blocks * threads / (best * 1e-3);
+    }
     return GL_OK;
 }
 

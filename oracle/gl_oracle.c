@@ -74,6 +74,7 @@ int glo_num_threads(void)
     return 1;
 #endif
 }
+void glo_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 /* -------------------------------------------------------------------- NTT */
 

@@ -63,6 +63,7 @@ void glo_fri_transpose(uint64_t *aux, const uint64_t *pol, uint64_t degree, unsi
 /* xorshift64 synthetic input of SURVEY 8(c)/(d): seed 88172645463325252, value = s mod p */
 void glo_fill_xorshift(uint64_t *dst, uint64_t count, uint64_t *state);
 int glo_num_threads(void);
+void glo_set_num_threads(int n);
 #ifdef __cplusplus
 }
 #endif

@@ -63,7 +63,7 @@ class _Oracle:
             ("glo_q_extend", None, [_u64p, _u64p, u64, u64, u64, u64]),
             ("glo_fri_fold", None, [_u64p, _u64p, C.c_uint, C.c_uint, u64, _u64p]),
             ("glo_fri_transpose", None, [_u64p, _u64p, u64, C.c_uint]),
-            ("glo_num_threads", C.c_int, []),
+            ("glo_num_threads", C.c_int, []), ("glo_set_num_threads", None, [C.c_int]),
         ]:
             f = getattr(L, name)
             f.restype = res
@@ -160,7 +160,7 @@ class _Ref:
         L = C.CDLL(path)
         u64 = C.c_uint64
         for name, res, args in [
-            ("ref_num_threads", C.c_int, []), ("ref_has_avx512", C.c_int, []),
+            ("ref_num_threads", C.c_int, []), ("ref_has_avx512", C.c_int, []), ("ref_set_num_threads", None, [C.c_int]),
             ("ref_ntt", None, [_u64p, _u64p, u64, u64, u64, u64]),
             ("ref_intt", None, [_u64p, _u64p, u64, u64, u64, u64]),
             ("ref_extend_pol", None, [_u64p, _u64p, u64, u64, u64, _u64p]),

@@ -22,6 +22,8 @@ typedef Goldilocks::Element E;
 extern "C" {
 
 int ref_num_threads(void) { return omp_get_max_threads(); }
+// torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the CPU arms of bench.py set the count explicitly
+void ref_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 int ref_has_avx512(void)
 {
