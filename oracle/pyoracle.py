@@ -274,6 +274,24 @@ class _Ref:
         return lde, tree, a.value, b.value
 
 
+class _RefBctree:
+    """interpolate() of the reference's offline constant-tree tool (tools/starkpil/bctree/build_const_tree.cpp:198-330),
+    compiled where it lies by oracle/Makefile (oracle/_ref/libglref_bctree.so): a second, independent LDE implementation."""
+
+    def __init__(self, path):
+        L = C.CDLL(path)
+        L.ref_bctree_interpolate.restype = None
+        L.ref_bctree_interpolate.argtypes = [_u64p, _u64p, C.c_uint64, C.c_uint64, C.c_uint64]
+        self.L = L
+
+    def interpolate(self, src, n_ext):
+        src = np.ascontiguousarray(src, dtype=np.uint64).copy()
+        n, npols = src.shape
+        out = np.zeros((n_ext, npols), dtype=np.uint64)
+        self.L.ref_bctree_interpolate(_p(out), _p(src), npols, int(n).bit_length() - 1, int(n_ext).bit_length() - 1)
+        return _Ref.canon(out)
+
+
 def _cpu_has(flag):
     try:
         with open("/proc/cpuinfo") as f:
@@ -309,3 +327,17 @@ def ref(prefer_avx512=False):
             except OSError:
                 _ref[kind] = None
     return _ref[kind]
+
+
+_bctree = []
+
+
+def ref_bctree():
+    """The reference bctree tool's interpolate(), or None when oracle/_ref/libglref_bctree.so was never built."""
+    if not _bctree:
+        path = os.path.join(HERE, "_ref", "libglref_bctree.so")
+        try:
+            _bctree.append(_RefBctree(path) if os.path.exists(path) and _cpu_has("avx2") else None)
+        except OSError:
+            _bctree.append(None)
+    return _bctree[0]

@@ -57,6 +57,9 @@ def fixtures():
         x = rng2.integers(0, P, size=3, dtype=np.uint64)
         si = int(rng2.integers(1, P, dtype=np.uint64))
         inputs["frifold_%d_%d" % (pb, nb)] = (pol, x, si)
+    rng3 = np.random.default_rng(meta.get("seed3", 0))
+    for (n, e, c) in meta.get("bctree", []):
+        inputs["bctree_%d_%d_%d" % (n, e, c)] = rng3.integers(0, P, size=(n, c), dtype=np.uint64)
     return {"out": fx, "in": inputs, "meta": meta}
 
 
