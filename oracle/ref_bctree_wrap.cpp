@@ -19,6 +19,9 @@ void *copyFile(const std::string &, uint64_t) { abort(); }
 
 extern "C" void ref_bctree_interpolate(uint64_t *dst, uint64_t *src, uint64_t nPols, uint64_t nBits, uint64_t nBitsExt)
 {
+    // the tool sizes its blocks from omp_get_max_threads() / 2 and divides by it (:170, :208): with an OpenMP team of one
+    // (e.g. after NTT_Goldilocks(nX, 1) of the FRI fold called omp_set_num_threads(1), ntt_goldilocks.cpp:59) it divides by zero
+    if (omp_get_max_threads() < 2) omp_set_num_threads(2);
     std::ostringstream sink; // interpolate() logs its phases to std::cout
     std::streambuf *old = std::cout.rdbuf(sink.rdbuf());
     interpolate((Goldilocks::Element *)src, nPols, nBits, (Goldilocks::Element *)dst, nBitsExt);

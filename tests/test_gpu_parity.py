@@ -365,6 +365,23 @@ def test_consttree_image(glb, oracle):
 
 
 @pytest.mark.gpu
+def test_consttree_image_vs_bctree_tool(glb, oracle, ref, fixtures):
+    """gl_build_consttree_host against the reference tool itself: the extended constants must equal the stored outputs of
+    interpolate() of tools/starkpil/bctree/build_const_tree.cpp:198-330 (compiled where it lies, tests/golden/make_golden.py),
+    the nodes the reference's PoseidonGoldilocks::merkletree over them (:366) and the last 4 words the verification key (:386-392)."""
+    cpu = ref if ref is not None else oracle
+    for (n, e, c) in fixtures["meta"]["bctree"]:
+        k = "bctree_%d_%d_%d" % (n, e, c)
+        img = glb.build_consttree_host(fixtures["in"][k], e)
+        want = fixtures["out"][k]
+        assert img[0] == c and img[1] == e, k
+        assert np.array_equal(img[2:2 + c * e].reshape(e, c), want), k
+        tree = cpu.merkletree(want)
+        assert np.array_equal(img[2 + c * e:], tree), k
+        assert np.array_equal(img[-4:], tree[-4:]), k
+
+
+@pytest.mark.gpu
 def test_cpp_shims_run_reference_tests(glb):
     """host/test_shims: the reference's gtest cases (tests.cpp merkletree/ntt/extendePol + the starks.cpp:52-56 sequence)
     compiled against the drop-in C++ classes (NTT_Goldilocks, MerkleTreeGL, PoseidonGoldilocks) over the C ABI."""

@@ -151,3 +151,17 @@ def test_fri_transpose_is_the_reference_index_map(oracle):
     for i in range(w):
         for j in range(h):
             assert np.array_equal(aux[i * h + j], pol[j * w + i])
+
+
+def test_bctree_interpolate_pins_the_oracle(oracle, fixtures):
+    """interpolate() of the reference's own bctree tool (tools/starkpil/bctree/build_const_tree.cpp:198-330,
+    a second LDE implementation: own block FFT, interpolatePrepare with shift^i / N) -- stored outputs, and run live when
+    oracle/_ref/libglref_bctree.so exists here -- equals the oracle's extendPol restatement word for word."""
+    from oracle import pyoracle
+    live = pyoracle.ref_bctree()
+    for (n, e, c) in fixtures["meta"]["bctree"]:
+        k = "bctree_%d_%d_%d" % (n, e, c)
+        x = fixtures["in"][k]
+        assert np.array_equal(oracle.extend_pol(x, e), fixtures["out"][k]), k
+        if live is not None:
+            assert np.array_equal(live.interpolate(x, e), fixtures["out"][k]), k
