@@ -44,8 +44,22 @@ int gl_init(int device);
 void gl_shutdown(void);
 const char *gl_last_error(void);
 int gl_device_count(int *count);
-/* Upper bound (bytes) for the library's internal scratch arena; 0 = default (8 GiB). */
+/* Upper bound (bytes) for the library's internal scratch arena; 0 = default (32 GiB, and never more than half of the free device memory). */
 int gl_set_scratch_limit(size_t bytes);
+/* Resident stage (off by default).  When on, gl_extend_pol_host -- NTT_Goldilocks::extendPol of the shims -- also hashes the
+ * leaves and builds the tree while the extended matrix is being downloaded (the download hides it) and keeps the device copies
+ * of both, keyed by the HOST pointer of `out`.  The gl_merkletree_host (MerkleTreeGL::merkelize, starks.cpp:52-56) that follows
+ * on the same pointer and shape then only downloads the nodes: no 80 GB upload, no second hashing.  A sample of the host words is
+ * compared with the device copy first; a buffer the host has written into since falls back to the normal path.  One stage is
+ * resident at a time (the next gl_extend_pol_host / gl_commit_host replaces it); turning the mode off frees it. */
+int gl_set_resident(int on);
+/* Device pointers of the resident matrix / tree for queries (gl_group_proofs_dev, gl_rows_gather_dev); fails if `host_src` is
+ * not the resident matrix. */
+int gl_resident_query(const uint64_t *host_src, uint64_t ncols, uint64_t nrows, uint64_t **lde_dev, uint64_t **tree_dev);
+/* Which NTT pass kernel runs the multi-pass transforms: 0 (default) ntt::k_pass -- direct global loads, two CTAs per SM alternate their
+ * load and butterfly phases; 2 / 3 ntt::k_pass2 -- persistent CTAs fed by cp.async / TMA through a ring of 2 / 3 shared-memory tiles.
+ * Same results; kept selectable because their ranking is shape dependent. */
+int gl_set_ntt_variant(int variant);
 /* Number of CUDA kernels launched by this library since the last call with reset != 0. */
 uint64_t gl_kernel_launches(int reset);
 
@@ -117,7 +131,8 @@ int gl_hash_full_result_host(uint64_t *out, const uint64_t *in, uint64_t n);
 int gl_linear_hash_host(uint64_t out[4], const uint64_t *in, uint64_t size);
 
 /* Batched field arithmetic, Goldilocks::add/sub/mul (goldilocks_base_field_scalar.hpp:16-160):
- * op 0 add(a,b), 1 sub(a,b), 2 mul(a,b), 3 a*b+c, 4 add with canonical b, 5 a^2, 6 canonicalise a.
+ * op 0 add(a,b), 1 sub(a,b), 2 mul(a,b), 3 a*b+c, 4 add with canonical b, 5 a^2, 6 canonicalise a,
+ * 7 / 8 / 9: the add / sub / canonicalise forms used inside the NTT butterflies (same values as 0 / 1 / 6).
  * out[i] is canonical.  b / c may be NULL when the op does not use them. */
 int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const uint64_t *c, uint64_t n, int op);
 

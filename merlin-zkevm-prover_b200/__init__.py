@@ -19,7 +19,8 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libglb200.so")
+# GLB_LIB selects another build of the same C ABI (A/B runs of kernel variants under tools/); the product is libglb200.so
+LIB_PATH = os.environ.get("GLB_LIB") or os.path.join(HERE, "libglb200.so")
 P = 0xFFFFFFFF00000001
 
 _u64p = C.POINTER(C.c_uint64)
@@ -32,6 +33,9 @@ SIGNATURES = {
     "gl_last_error": (C.c_char_p, []),
     "gl_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "gl_set_scratch_limit": (C.c_int, [C.c_size_t]),
+    "gl_set_resident": (C.c_int, [C.c_int]),
+    "gl_set_ntt_variant": (C.c_int, [C.c_int]),
+    "gl_resident_query": (C.c_int, [_u64p, _u64, _u64, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "gl_kernel_launches": (_u64, [C.c_int]),
     "gl_dev_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "gl_dev_free": (C.c_int, [C.c_void_p]),
@@ -328,7 +332,7 @@ def linear_hash_host(inp):
     return out
 
 
-FIELD_OPS = {"add": 0, "sub": 1, "mul": 2, "mad": 3, "add_c": 4, "sqr": 5, "canon": 6}
+FIELD_OPS = {"add": 0, "sub": 1, "mul": 2, "mad": 3, "add_c": 4, "sqr": 5, "canon": 6, "add_cx": 7, "sub_cx": 8, "canon_sel": 9, "sqr3": 10}
 
 
 def field_op_host(op, a, b=None, c=None):

@@ -189,6 +189,28 @@ __device__ __forceinline__ u128 mul_wide_native(u64 a, u64 b)
 }
 __device__ __forceinline__ u64 mul(u64 a, u64 b) { return reduce128(mul_wide_native(a, b)); }
 __device__ __forceinline__ u64 sqr(u64 a) { return reduce128(mul_wide_native(a, a)); }
+// a^2 with THREE 32 x 32 products (a0^2 + 2 a0 a1 2^32 + a1^2 2^64) instead of the four ptxas emits for a * a: one IMAD.WIDE (4 clocks,
+// nothing issues beside it) traded for ~4 ALU-pipe instructions that double the cross product.  A/B switch for the Poseidon S-box
+// (GLB_POSEIDON_SQR3); tests/test_gpu_parity.py::test_field_ops checks the value as op "sqr3".
+__device__ __forceinline__ u64 sqr3(u64 a)
+{
+    const u32 a0 = (u32)a, a1 = (u32)(a >> 32);
+    const u64 p0 = (u64)a0 * a0, p2 = (u64)a1 * a1, c = (u64)a0 * a1;
+    u128 r;
+    asm("{\n\t"
+        ".reg .u32 d0, d1, d2;\n\t"
+        "shl.b32 d0, %6, 1;\n\t"
+        "shf.l.wrap.b32 d1, %6, %7, 1;\n\t"
+        "shr.b32 d2, %7, 31;\n\t"
+        "add.cc.u32 %1, %4, d0;\n\t"
+        "addc.cc.u32 %2, %5, d1;\n\t"
+        "addc.u32 %3, %8, d2;\n\t"
+        "mov.u32 %0, %9;\n\t"
+        "}"
+        : "=r"(r.x0), "=r"(r.x1), "=r"(r.x2), "=r"(r.x3)
+        : "r"((u32)(p0 >> 32)), "r"((u32)p2), "r"((u32)c), "r"((u32)(c >> 32)), "r"((u32)(p2 >> 32)), "r"((u32)p0));
+    return reduce128(r);
+}
 // a*b + c  (fused: the addend rides on the first partial product)
 __device__ __forceinline__ u64 mad(u64 a, u64 b, u64 c) { return reduce128(mad_wide(a, b, c)); }
 // the same three with the ALU-only reduction (round-2 experiment, see reduce128_alu)
@@ -249,6 +271,72 @@ __device__ __forceinline__ u64 canon(u64 x)
         "}"
         : "=&r"(r0), "=&r"(r1)
         : "r"((u32)x), "r"((u32)(x >> 32)), "r"(c_eps[0]));
+    return pack(r0, r1);
+}
+
+// ---- pipe-balanced forms for the NTT passes ------------------------------------------------------------------------------
+// Measured issue model of the B200 SM sub-partition (profiles/r2_01_ubench_pipes.txt): an IMAD.WIDE.U32 takes 4 clocks and nothing
+// issues beside it; every other integer instruction takes 2 clocks on its pipe -- IADD3 / LOP3 / SHF / SEL / ISETP on the ALU pipe,
+// the 32-bit IMAD forms (IMAD, IMAD.X = multiply-add with carry-in) on the IMAD pipe -- and the two pipes run side by side.
+// ptxas puts nearly all carry arithmetic on the ALU pipe, which then carries 2.4x the load of the IMAD pipe in the NTT pass and
+// bounds it.  The forms below keep on the ALU pipe only what needs a carry-OUT (IADD3 is the one instruction that has it) and write
+// every carry-consuming chain end and every mask / negation as a multiply-add (madc.lo / mul.lo -> IMAD.X / IMAD), and they use no
+// IMAD.WIDE for the conditional +-(2^32 - 1).  One butterfly (canon_sel + add_cx + sub_cx) is 10 ALU + 9 IMAD + 0 IMAD.WIDE against
+// 10 ALU + 1 IMAD + 2 IMAD.WIDE for canon + add_c + sub_c: 21 against 29 clocks in the measured model (tools/sass_cost.py).  The same
+// treatment of the multiplication's reduction does NOT pay (ptxas already folds its sign handling into LEA.HI.X: 69 against 62 ALU
+// instructions per 8 products), so gl::mul and mul_pow2 stay as they are.  gl_field_op_host ops 7-9 check the values.
+
+// x mod p:  x >= p  <=>  x + (2^32 - 1) carries; then x - p = x + (2^32 - 1) - 2^64.          ALU 3, IMAD 3, no IMAD.WIDE
+__device__ __forceinline__ u64 canon_sel(u64 x)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 t, k, m;\n\t"
+        "add.cc.u32 t, %2, 0xFFFFFFFF;\n\t"
+        "addc.cc.u32 t, %3, 0;\n\t"
+        "madc.lo.u32 k, 0, 0, 0;\n\t"               // k = carry
+        "mul.lo.u32 m, k, 0xFFFFFFFF;\n\t"          // m = -k
+        "add.cc.u32 %0, %2, m;\n\t"
+        "madc.lo.u32 %1, %3, 1, 0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)x), "r"((u32)(x >> 32)));
+    return pack(r0, r1);
+}
+// a + b, b canonical:  s + carry * (2^32 - 1) = {s1, s0 + m} with m = -carry and the carry of the low word into s1.   ALU 3, IMAD 3
+__device__ __forceinline__ u64 add_cx(u64 a, u64 b)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 k, m;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\t"
+        "addc.cc.u32 %1, %3, %5;\n\t"
+        "madc.lo.u32 k, 0, 0, 0;\n\t"
+        "mul.lo.u32 m, k, 0xFFFFFFFF;\n\t"
+        "add.cc.u32 %0, %0, m;\n\t"
+        "madc.lo.u32 %1, %1, 1, 0;\n\t"
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    return pack(r0, r1);
+}
+// a - b, b canonical:  d - borrow * (2^32 - 1) = {d1 + m, d0 + k} with m = -borrow, k = borrow.                      ALU 3-4, IMAD 2-3
+// (The borrow is taken out of the subtract chain with subc and only ADD chains feed madc: ptxas hands madc the hardware carry, which
+// after sub.cc is the complement of the borrow PTX documents -- a subtract chain must not end in a madc.)
+__device__ __forceinline__ u64 sub_cx(u64 a, u64 b)
+{
+    u32 r0, r1;
+    asm("{\n\t"
+        ".reg .u32 m, k;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\t"
+        "subc.cc.u32 %1, %3, %5;\n\t"
+        "subc.u32 m, 0, 0;\n\t"                     // m = -borrow (0 or 0xFFFFFFFF)
+        "mul.lo.u32 k, m, 0xFFFFFFFF;\n\t"          // k = borrow
+        "add.cc.u32 %0, %0, k;\n\t"
+        "madc.lo.u32 %1, %1, 1, m;\n\t"             // d1 - borrow + carry
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
     return pack(r0, r1);
 }
 

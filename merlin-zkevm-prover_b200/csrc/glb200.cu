@@ -5,6 +5,7 @@
 // point fails with GL_ERR_CUDA when no device is usable.
 #include "../../include/gl_commit.h"
 #include "ntt.cuh"
+#include "ntt2.cuh"
 #include "poseidon_kernels.cuh"
 #include "fri.cuh"
 
@@ -15,6 +16,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -65,9 +67,18 @@ struct Ctx {
     size_t arena_bytes = 0;
     u64 *roots = nullptr, *rscale = nullptr; // twiddle / coset-scale tables (device)
     u32 log_roots = 0, log_rscale = 0;
-    size_t scratch_limit = (size_t)8 << 30;
+    size_t scratch_limit = (size_t)32 << 30; // upper bound; pick_col_block also stays within half of the free device memory
     std::atomic<uint64_t> launches{0};
     float ms[4] = {0, 0, 0, 0}; // LDE, leaf hashing, tree levels, multi-GPU exchange
+    // Resident stage (opt-in, gl_set_resident): the device copies of the last gl_extend_pol_host output and of the tree hashed
+    // over it while it was being downloaded, keyed by the HOST pointer the caller got the matrix in.
+    bool resident_on = false;
+    const void *res_host = nullptr;
+    u64 res_rows = 0, res_cols = 0;
+    void *res_lde = nullptr, *res_tree = nullptr;
+    int ntt_variant = 0;        // 0: k_pass (direct loads, two CTAs per SM alternate load and butterfly phases -- the faster one),
+                                // 2 / 3: k_pass2 (ntt2.cuh: TMA / cp.async ring of 2 / 3 tile buffers); env GLB_NTT or gl_set_ntt_variant
+    int sms = 148;
     u64 *qbuf = nullptr;        // grow-only staging of the batched query calls: [indices | gathered words] (device)
     size_t qbuf_words = 0;
     std::mutex mu;
@@ -209,10 +220,10 @@ int launch_pass_cw(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
 {
     constexpr int R = 16 << B2;
     size_t smem = B2 > 0 ? (size_t)R * ntt::kTileCols * 8 : 0;
-    static bool attr_done = false;
-    if (!attr_done && smem > 48 * 1024) {
+    static bool attr_done[16] = {false}; // per device: the attribute belongs to the device's copy of the function
+    if (!attr_done[g.device & 15] && smem > 48 * 1024) {
         CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
+        attr_done[g.device & 15] = true;
     }
     dim3 grid((unsigned)(ntiles / (ntt::kTileCols / CW)), coltiles), block(32, 1 << B2);
     ntt::k_pass<B2, LAST, CW><<<grid, block, smem, g.stream>>>(p);
@@ -266,6 +277,76 @@ int launch_pass(const ntt::PassParams &p)
     return fail(GL_ERR_ARG, "bad pass width %u", b);
 }
 
+// ---- k_pass2 (ntt2.cuh): persistent CTAs, tiles fed by cp.async (first pass) / TMA (other passes) ----------------------------
+template <int B2, int MODE, int NBUF>
+int launch_pass2_inst(const ntt::Pass2Params &p, const CUtensorMap &in_map, const CUtensorMap &out_map)
+{
+    auto kern = ntt::k_pass2<B2, MODE, NBUF, GLB_NTT_CSEL != 0>;
+    const size_t smem = ntt::pass2_smem<B2, NBUF>();
+    static int occ[16] = {0}; // per device: resident CTAs per SM
+    int &o = occ[g.device & 15];
+    if (o == 0) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, 16 << B2, smem));
+        if (o < 1) return fail(GL_ERR_CUDA, "k_pass2<%d,%d,%d> does not fit an SM", B2, MODE, NBUF);
+    }
+    u64 grid = (u64)g.sms * o;
+    if (grid > p.nstrips) grid = p.nstrips;
+    kern<<<(unsigned)grid, 16 << B2, smem, g.stream>>>(in_map, out_map, p);
+    g.launches++;
+    CU(cudaGetLastError());
+    return GL_OK;
+}
+template <int B2, int MODE>
+int launch_pass2_b(const ntt::Pass2Params &p, const CUtensorMap &in_map, const CUtensorMap &out_map, int nbuf)
+{
+    if (nbuf == 3) return launch_pass2_inst<B2, MODE, 3>(p, in_map, out_map);
+    return launch_pass2_inst<B2, MODE, 2>(p, in_map, out_map);
+}
+template <int MODE>
+int launch_pass2_m(const ntt::Pass2Params &p, const CUtensorMap &in_map, const CUtensorMap &out_map, int nbuf)
+{
+    switch (p.bits[p.pass]) {
+    case 5: return launch_pass2_b<1, MODE>(p, in_map, out_map, nbuf);
+    case 6: return launch_pass2_b<2, MODE>(p, in_map, out_map, nbuf);
+    case 7: return launch_pass2_b<3, MODE>(p, in_map, out_map, nbuf);
+    case 8: return launch_pass2_b<4, MODE>(p, in_map, out_map, nbuf);
+    }
+    return fail(GL_ERR_ARG, "k_pass2: bad pass width %u", p.bits[p.pass]);
+}
+
+// The new passes need: >= 2 passes, every pass 5..8 bits wide, and a scratch block a tensor map can describe (16-byte aligned base,
+// even pitch, padded to whole 16-column tiles).
+bool pass2_usable(u32 logn, u32 m, const u32 *bits, const u64 *tmp, u64 tpitch, u32 ncols)
+{
+    if (g.ntt_variant == 0 || m < 2 || !tmp) return false;
+    for (u32 i = 0; i < m; i++)
+        if (bits[i] < 5 || bits[i] > 8) return false;
+    if (((uintptr_t)tmp & 15) || (tpitch & 1) || ((ncols + 15) & ~15u) > tpitch) return false;
+    (void)logn;
+    return true;
+}
+
+int launch_pass2(const ntt::PassParams &pp)
+{
+    ntt::Pass2Params p;
+    memcpy(static_cast<ntt::PassParams *>(&p), &pp, sizeof(ntt::PassParams));
+    const u32 b = p.bits[p.pass];
+    p.nstrips = (1ULL << p.logn) >> b;
+    p.coltiles = (p.ncols + ntt::kW2 - 1) / ntt::kW2;
+    const bool first = p.pass == 0, last = p.pass + 1 == p.npass;
+    const u64 n = 1ULL << p.logn, wpad = (u64)p.coltiles * ntt::kW2;
+    CUtensorMap in_map, out_map;
+    memset(&in_map, 0, sizeof in_map);
+    memset(&out_map, 0, sizeof out_map);
+    if (!first && tma::make_map_3d(&in_map, p.src, p.spitch, wpad, n, p.log_rest, ntt::kW2, 1u << b)) return fail(GL_ERR_CUDA, "cuTensorMapEncodeTiled failed (pass input)");
+    if (!last && tma::make_map_4d(&out_map, p.dst, p.dpitch, wpad, n, p.log_rest, ntt::kW2, 1u << (b - 4))) return fail(GL_ERR_CUDA, "cuTensorMapEncodeTiled failed (pass output)");
+    const int nbuf = g.ntt_variant == 3 ? 3 : 2;
+    if (first) return launch_pass2_m<ntt::kFirst>(p, in_map, out_map, nbuf);
+    if (last) return launch_pass2_m<ntt::kLast>(p, in_map, out_map, nbuf);
+    return launch_pass2_m<ntt::kMid>(p, in_map, out_map, nbuf);
+}
+
 // One transform of `ncols` columns (ncols small enough for tmp).  src/dst may alias.
 // scale_mode: 0 none, 1: 1/n, 2: 7^i/n.  nvalid: rows >= nvalid of src are zeros.
 int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpitch, u32 logn, u32 ncols,
@@ -293,6 +374,7 @@ int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpit
     p.log_roots = g.log_roots;
     p.rscale = g.rscale;
     p.cscale = scale_mode == 1 ? hpow((P + 1) / 2, logn) : 1; // 2^-logn (1: unscaled)
+    const bool v2 = pass2_usable(logn, m, p.bits, tmp, tpitch, ncols);
     u32 prev = 0;
     for (u32 i = 0; i < m; i++) {
         p.pass = i;
@@ -305,20 +387,29 @@ int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpit
         p.dpitch = last ? dpitch : tpitch;
         p.nvalid = first ? nvalid : (1ULL << logn);
         p.scale_mode = last ? scale_mode : 0;
-        TRY(launch_pass(p));
+        TRY(v2 ? launch_pass2(p) : launch_pass(p));
         prev += p.bits[i];
     }
     return GL_OK;
 }
 
+// Columns per scratch block: as many as the scratch limit and half of the free device memory allow (wide blocks amortise the
+// per-strip twiddle gather of k_pass2 and the launch tails), a multiple of 32, at least 32.
 u32 pick_col_block(u64 ncols, size_t bytes_per_col)
 {
-    u64 cb = g.scratch_limit / bytes_per_col;
+    size_t budget = g.scratch_limit, free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+        free_b += g.arena_bytes; // the arena is ours to reuse
+        if (free_b / 2 < budget) budget = free_b / 2;
+    }
+    u64 cb = budget / bytes_per_col;
     cb = (cb / 32) * 32;
     if (cb < 32) cb = 32;
     if (cb > ncols) cb = ncols;
     return (u32)cb;
 }
+// scratch pitch of a block of cb columns: whole 16-column tiles (tensor maps need an even pitch; k_pass2 reads / writes whole tiles)
+u64 pad16(u64 cb) { return (cb + 15) & ~(u64)15; }
 
 int ntt_dev(u64 *dst, const u64 *src, u64 size, u64 ncols, int inverse, int extend)
 {
@@ -329,10 +420,11 @@ int ntt_dev(u64 *dst, const u64 *src, u64 size, u64 ncols, int inverse, int exte
     u32 logn = ilog2(size);
     int mode = inverse ? (extend ? 2 : 1) : 0;
     u32 cb = pick_col_block(ncols, size * 8);
-    if (logn > 8) TRY(arena_reserve((size_t)size * cb * 8));
+    const u64 cp = pad16(cb);
+    if (logn > 8) TRY(arena_reserve((size_t)size * cp * 8));
     for (u64 c0 = 0; c0 < ncols; c0 += cb) {
         u32 w = (u32)((ncols - c0 < cb) ? ncols - c0 : cb);
-        TRY(run_ntt(dst + c0, ncols, src + c0, ncols, (u64 *)g.arena, cb, logn, w, inverse != 0, mode, size));
+        TRY(run_ntt(dst + c0, ncols, src + c0, ncols, (u64 *)g.arena, cp, logn, w, inverse != 0, mode, size));
     }
     return GL_OK;
 }
@@ -344,13 +436,14 @@ int extend_pol_dev(u64 *out, const u64 *in, u64 n_ext, u64 n, u64 ncols)
     if (n_ext > (1ULL << 32)) return fail(GL_ERR_RANGE, "Domain size too big for the curve");
     u32 logn = ilog2(n), loge = ilog2(n_ext);
     u32 cb = pick_col_block(ncols, (n + n_ext) * 8);
-    TRY(arena_reserve((size_t)(n + n_ext) * cb * 8));
-    u64 *coef = (u64 *)g.arena;          // n x cb      INTT result, scaled by 7^i / n
-    u64 *tmp = coef + (size_t)n * cb;    // n_ext x cb  pass scratch
+    const u64 cp = pad16(cb);
+    TRY(arena_reserve((size_t)(n + n_ext) * cp * 8));
+    u64 *coef = (u64 *)g.arena;          // n x cp      INTT result, scaled by 7^i / n
+    u64 *tmp = coef + (size_t)n * cp;    // n_ext x cp  pass scratch
     for (u64 c0 = 0; c0 < ncols; c0 += cb) {
         u32 w = (u32)((ncols - c0 < cb) ? ncols - c0 : cb);
-        TRY(run_ntt(coef, cb, in + c0, ncols, tmp, cb, logn, w, true, 2, n));
-        TRY(run_ntt(out + c0, ncols, coef, cb, tmp, cb, loge, w, false, 0, n));
+        TRY(run_ntt(coef, cp, in + c0, ncols, tmp, cp, logn, w, true, 2, n));
+        TRY(run_ntt(out + c0, ncols, coef, cp, tmp, cp, loge, w, false, 0, n));
     }
     return GL_OK;
 }
@@ -472,6 +565,10 @@ __global__ void k_field_op(u64 *out, const u64 *a, const u64 *b, const u64 *c, u
     case 3: r = gl::mad(a[i], b[i], c[i]); break;
     case 4: r = gl::add_c(a[i], gl::canon(b[i])); break;
     case 5: r = gl::sqr(a[i]); break;
+    case 7: r = gl::add_cx(a[i], gl::canon_sel(b[i])); break;
+    case 8: r = gl::sub_cx(a[i], gl::canon_sel(b[i])); break;
+    case 9: r = gl::canon_sel(a[i]); break;
+    case 10: r = gl::sqr3(a[i]); break;
     default: r = a[i];
     }
     out[i] = gl::canon(r);
@@ -573,9 +670,19 @@ __global__ void k_fill_synthetic_cols(u64 *dst, u64 nrows, u64 col0, u64 w, u64 
     }
 }
 
+void resident_drop()
+{
+    if (g.res_lde) cudaFree(g.res_lde);
+    if (g.res_tree) cudaFree(g.res_tree);
+    g.res_lde = g.res_tree = nullptr;
+    g.res_host = nullptr;
+    g.res_rows = g.res_cols = 0;
+}
+
 struct DevBuf {
     void *p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
+    void *release() { void *q = p; p = nullptr; return q; }
     int alloc(size_t bytes)
     {
         CU(cudaMalloc(&p, bytes ? bytes : 8));
@@ -591,8 +698,9 @@ struct DevBuf {
 // Host buffers should be pinned (gl_host_alloc / gl_host_register) -- pageable memory still works but the
 // copies then serialise.
 int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t *in, u64 n_ext, u64 n, u64 ncols, uint64_t root[4],
-                          bool do_tree)
+                          bool do_tree, bool keep_resident = false)
 {
+    resident_drop(); // at most one resident stage: its 80 GB would not fit twice
     if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "extendPol: bad sizes %llu -> %llu", n, n_ext);
     if (n_ext > (1ULL << 32)) return fail(GL_ERR_RANGE, "Domain size too big for the curve");
     const u32 logn = ilog2(n), loge = ilog2(n_ext);
@@ -610,9 +718,10 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         const size_t per_col = (size_t)(3 * n + n_ext) * 8; // coef + pass scratch + two staging buffers
         while (cb > 32 && per_col * cb + ((size_t)1 << 30) > free_b) cb -= 32;
         if (cb > ncols) cb = ncols;
-        TRY(arena_reserve((size_t)(n + n_ext) * cb * 8));
+        const u64 cp = pad16(cb);
+        TRY(arena_reserve((size_t)(n + n_ext) * cp * 8));
         TRY(stage.alloc((size_t)2 * n * cb * 8));
-        u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cb;
+        u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cp;
         // block boundaries: a narrow first block so that compute starts after a short upload, then full-width blocks
         std::vector<u64> starts;
         const bool graded = cb > 32 && ncols > 2 * cb;
@@ -636,8 +745,8 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
             cudaMemcpy2DAsync(st, cb * 8, in + c0, ncols * 8, (size_t)w * 8, n, cudaMemcpyHostToDevice, g.s_h2d);
             cudaEventRecord(ev_in[k], g.s_h2d);
             cudaStreamWaitEvent(g.stream, ev_in[k], 0);
-            rc = run_ntt(coef, cb, st, cb, tmp, cb, logn, w, true, 2, n);
-            if (rc == GL_OK) rc = run_ntt(lde + c0, ncols, coef, cb, tmp, cb, loge, w, false, 0, n);
+            rc = run_ntt(coef, cp, st, cb, tmp, cp, logn, w, true, 2, n);
+            if (rc == GL_OK) rc = run_ntt(lde + c0, ncols, coef, cp, tmp, cp, loge, w, false, 0, n);
             cudaEventRecord(ev_done[k], g.stream);
             if (do_tree && ncols > 4 && rc == GL_OK) { // hash this block's columns now; the capacity words wait in the leaf slots
                 poseidon::k_linear_hash_partial<<<poseidon::grid_for(n_ext), poseidon::kThreads, 0, g.stream>>>((u64 *)t.p, lde, n_ext, ncols, (u32)c0, w);
@@ -671,7 +780,36 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
     CU(cudaStreamSynchronize(g.stream));
     CU(cudaStreamSynchronize(g.s_d2h));
     CU(cudaStreamSynchronize(g.s_h2d));
+    if (keep_resident && lde_out && do_tree) {
+        g.res_host = lde_out;
+        g.res_rows = n_ext;
+        g.res_cols = ncols;
+        g.res_lde = l.release();
+        g.res_tree = t.release();
+    }
     return GL_OK;
+}
+
+// Is `src` (nrows x ncols, host) the matrix whose device copy is resident?  The pointer and the shape must match and a sample
+// of its words must still equal the device copy (the host side may have written into the buffer since: then the copy is stale).
+bool resident_matches(const uint64_t *src, u64 ncols, u64 nrows)
+{
+    if (!g.resident_on || !g.res_lde || src != g.res_host || nrows != g.res_rows || ncols != g.res_cols) return false;
+    const u64 words = nrows * ncols;
+    if (words == 0) return true;
+    uint64_t probe[64];
+    for (int i = 0; i < 64; i++) {
+        const u64 at = i == 63 ? words - 1 : (words / 64) * i + (i * 7919ULL) % (words / 64 ? words / 64 : 1);
+        if (cudaMemcpyAsync(&probe[i], (const u64 *)g.res_lde + at, 8, cudaMemcpyDeviceToHost, g.stream) != cudaSuccess) return false;
+    }
+    if (cudaStreamSynchronize(g.stream) != cudaSuccess) return false;
+    for (int i = 0; i < 64; i++) {
+        const u64 at = i == 63 ? words - 1 : (words / 64) * i + (i * 7919ULL) % (words / 64 ? words / 64 : 1);
+        u64 h = src[at];
+        if (h >= P) h -= P; // the device copy is canonical
+        if (h != probe[i]) return false;
+    }
+    return true;
 }
 
 } // namespace
@@ -699,6 +837,8 @@ int gl_init(int device)
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10) return fail(GL_ERR_CUDA, "device %s is sm_%d%d; this library is built for sm_100a only", prop.name, prop.major, prop.minor);
+    g.sms = prop.multiProcessorCount;
+    if (const char *v = getenv("GLB_NTT")) g.ntt_variant = atoi(v);
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
@@ -722,6 +862,7 @@ void gl_shutdown(void)
     g.arena_bytes = 0;
     if (g.roots) cudaFree(g.roots);
     if (g.rscale) cudaFree(g.rscale);
+    resident_drop();
     if (g.qbuf) cudaFree(g.qbuf);
     g.qbuf = nullptr;
     g.qbuf_words = 0;
@@ -738,9 +879,33 @@ void gl_shutdown(void)
     g.device = -1;
 }
 
+int gl_set_resident(int on)
+{
+    std::lock_guard<std::recursive_mutex> api_lock_(g_api_mu);
+    g.resident_on = on != 0;
+    if (!g.resident_on && g.ready) resident_drop();
+    return GL_OK;
+}
+
+int gl_resident_query(const uint64_t *host_src, uint64_t ncols, uint64_t nrows, uint64_t **lde_dev, uint64_t **tree_dev)
+{
+    API_ENTER();
+    const bool ok = resident_matches(host_src, ncols, nrows);
+    if (lde_dev) *lde_dev = ok ? (uint64_t *)g.res_lde : nullptr;
+    if (tree_dev) *tree_dev = ok ? (uint64_t *)g.res_tree : nullptr;
+    return ok ? GL_OK : fail(GL_ERR_ARG, "no resident copy of this matrix");
+}
+
+int gl_set_ntt_variant(int v)
+{
+    if (v != 0 && v != 2 && v != 3) return fail(GL_ERR_ARG, "NTT pass variant %d (0: k_pass, 2 / 3: k_pass2 with 2 / 3 tile buffers)", v);
+    g.ntt_variant = v;
+    return GL_OK;
+}
+
 int gl_set_scratch_limit(size_t bytes)
 {
-    g.scratch_limit = bytes ? bytes : ((size_t)8 << 30);
+    g.scratch_limit = bytes ? bytes : ((size_t)32 << 30);
     return GL_OK;
 }
 
@@ -1002,6 +1167,9 @@ int gl_extend_pol_host(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64
 {
     if (n == 0 || ncols == 0) return GL_OK;
     API_ENTER();
+    // resident mode: hash the leaves while the extended matrix is on its way down (the download hides it) and keep both on the
+    // device, so that the MerkleTreeGL::merkelize() that follows (starks.cpp:52-56) neither uploads 80 GB nor hashes again
+    if (g.resident_on) return commit_host_pipelined(out, nullptr, in, n_ext, n, ncols, nullptr, true, true);
     return commit_host_pipelined(out, nullptr, in, n_ext, n, ncols, nullptr, false);
 }
 
@@ -1009,6 +1177,8 @@ int gl_merkletree_host(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint
 {
     if (nrows == 0) return GL_OK;
     API_ENTER();
+    if (resident_matches(src, ncols, nrows)) // the tree was built when this matrix was extended: only the nodes travel
+        return gl_d2h(tree, g.res_tree, gl_tree_num_elements(nrows) * 8);
     DevBuf s, t;
     TRY(s.alloc((size_t)nrows * ncols * 8));
     TRY(t.alloc(gl_tree_num_elements(nrows) * 8));
@@ -1094,7 +1264,7 @@ int gl_field_op_host(uint64_t *out, const uint64_t *a, const uint64_t *b, const 
 {
     if (n == 0) return GL_OK;
     API_ENTER();
-    if (op < 0 || op > 6) return fail(GL_ERR_ARG, "unknown field op %d", op);
+    if (op < 0 || op > 10) return fail(GL_ERR_ARG, "unknown field op %d", op);
     DevBuf d;
     TRY(d.alloc((size_t)n * 8 * 4));
     u64 *base = (u64 *)d.p;
@@ -1272,9 +1442,10 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
         const size_t per_col = (size_t)(3 * n + n_ext) * 8; // coef + pass scratch + two staging buffers
         while (cb > 32 && per_col * cb + ((size_t)1 << 30) > free_b) cb -= 32;
         if (cb > w) cb = w;
-        TRY(arena_reserve((size_t)(n + n_ext) * cb * 8));
+        const u64 cp = pad16(cb);
+        TRY(arena_reserve((size_t)(n + n_ext) * cp * 8));
         TRY(stage.alloc((size_t)2 * n * cb * 8));
-        u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cb;
+        u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cp;
         const u64 nb = (w + cb - 1) / cb;
         std::vector<cudaEvent_t> ev_in(nb), ev_done(nb);
         for (u64 k = 0; k < nb; k++) {
@@ -1290,8 +1461,8 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
             cudaMemcpy2DAsync(st, cb * 8, in_cols_host + c0, w * 8, (size_t)ww * 8, n, cudaMemcpyHostToDevice, g.s_h2d);
             cudaEventRecord(ev_in[k], g.s_h2d);
             cudaStreamWaitEvent(g.stream, ev_in[k], 0);
-            rc = run_ntt(coef, cb, st, cb, tmp, cb, logn, ww, true, 2, n);
-            if (rc == GL_OK) rc = run_ntt((u64 *)lde_cols + c0, w, coef, cb, tmp, cb, loge, ww, false, 0, n);
+            rc = run_ntt(coef, cp, st, cb, tmp, cp, logn, ww, true, 2, n);
+            if (rc == GL_OK) rc = run_ntt((u64 *)lde_cols + c0, w, coef, cp, tmp, cp, loge, ww, false, 0, n);
             cudaEventRecord(ev_done[k], g.stream);
         }
         cudaError_t e = cudaGetLastError();
@@ -1379,10 +1550,11 @@ int gl_q_extend_dev(uint64_t *cm4, const uint64_t *q_2ns, uint64_t n, uint64_t n
     CU(cudaGetLastError());
     // forward NTT over the extended domain; rows >= n of qq2 are zeros (:284)
     u32 cb = pick_col_block(w, n_ext * 8);
-    if (loge > 8) TRY(arena_reserve((size_t)n_ext * cb * 8));
+    const u64 cp = pad16(cb);
+    if (loge > 8) TRY(arena_reserve((size_t)n_ext * cp * 8));
     for (u64 c0 = 0; c0 < w; c0 += cb) {
         u32 ww = (u32)((w - c0 < cb) ? w - c0 : cb);
-        TRY(run_ntt((u64 *)cm4 + c0, w, (const u64 *)qq2.p + c0, w, (u64 *)g.arena, cb, loge, ww, false, 0, n));
+        TRY(run_ntt((u64 *)cm4 + c0, w, (const u64 *)qq2.p + c0, w, (u64 *)g.arena, cp, loge, ww, false, 0, n));
     }
     CU(cudaEventRecord(g.ev[1], g.stream));
     return collect_timings(true, false);

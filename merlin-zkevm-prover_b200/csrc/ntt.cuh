@@ -29,6 +29,10 @@ using gl::u32;
 using gl::u64;
 
 constexpr int kTileCols = 32;
+#ifndef GLB_NTT_CSEL
+#define GLB_NTT_CSEL 1 // butterflies in the IMAD.WIDE-free form (gl::canon_sel / add_cx / sub_cx); 0: the round-1 form, kept for A/B builds
+#endif
+constexpr bool kCsel = GLB_NTT_CSEL != 0;
 
 // Power tables (uploaded by the host at init):
 //   c_w32[j][i] = W32^(i * 2^(8j))   W32 = primitive 2^32-th root (reference Goldilocks::W[32])
@@ -86,7 +90,7 @@ __device__ __forceinline__ u64 mul_pow2_sel(u64 d, int sh)
 // (Goldilocks::W[1..6] = 2^96, 2^48, 2^24, 2^12, 2^6, 2^3; goldilocks_base_field.cpp:11-18), so a butterfly
 // is canon (4) + add (4) + sub (5) instructions and, for 17 of the 32 butterflies of a radix-16, a
 // 6-8 instruction shift-multiply.  Values stay lazily reduced; only the subtrahend is canonicalised.
-template <int LOG>
+template <int LOG, bool CSEL = false>
 __device__ __forceinline__ void dft_regs(u64 *x)
 {
     constexpr int N = 1 << LOG;
@@ -98,9 +102,9 @@ __device__ __forceinline__ void dft_regs(u64 *x)
 #pragma unroll
             for (int i = 0; i < half; i++) {
                 const int ia = blk * 2 * half + i, ib = ia + half;
-                const u64 a = x[ia], b = gl::canon(x[ib]);
-                x[ia] = gl::add_c(a, b);
-                const u64 d = gl::sub_c(a, b);
+                const u64 a = x[ia], b = CSEL ? gl::canon_sel(x[ib]) : gl::canon(x[ib]);
+                x[ia] = CSEL ? gl::add_cx(a, b) : gl::add_c(a, b);
+                const u64 d = CSEL ? gl::sub_cx(a, b) : gl::sub_c(a, b);
                 x[ib] = mul_pow2_sel(d, (192 / N) * (i << s)); // exponent of w_N: i << s < N/2
             }
         }
@@ -129,12 +133,12 @@ struct PassParams {
     u64 cscale;         // scale_mode 1: 1/n
 };
 
-template <int B2> struct Step2 {
+template <int B2, bool CSEL = false> struct Step2 {
     static __device__ __forceinline__ void run(u64 *y)
     {
         constexpr int R2 = 1 << B2;
 #pragma unroll
-        for (int g = 0; g < 16 / R2; g++) dft_regs<B2>(y + g * R2);
+        for (int g = 0; g < 16 / R2; g++) dft_regs<B2, CSEL>(y + g * R2);
     }
 };
 
@@ -180,7 +184,7 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     }
 
     // ---- step 1: radix-16 over i1 (row = (i1*R2 + t) within the tile)
-    dft_regs<4>(x);
+    dft_regs<4, kCsel>(x);
 
     if (B2 > 0) {
         // ---- twiddle w_R^(t*k1), exchange through shared memory, step 2: radix-R2 over t
@@ -194,7 +198,7 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < 16; i++) x[i] = tile[(16 * t + i) * kTileCols + c];
-        Step2<B2>::run(x);
+        Step2<B2, kCsel>::run(x);
     }
 
     // ---- store

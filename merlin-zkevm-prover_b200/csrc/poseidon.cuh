@@ -40,6 +40,9 @@ __device__ __forceinline__ constexpr u32 mds_entry(int j, int i)
     return circ[(i - j + 12) % 12] + ((i == 0 && j == 0) ? 8u : 0u);
 }
 
+#ifndef GLB_POSEIDON_SQR3
+#define GLB_POSEIDON_SQR3 1 // both squarings of the S-box with three 32 x 32 products (gl::sqr3): 1584 -> 1601 M perm/s (profiles/r2_08); 0: a * a
+#endif
 #ifndef GLB_POSEIDON_RED_ALU
 #define GLB_POSEIDON_RED_ALU 0 // round-2 experiment: 1 = S-box reductions, 2 = also the 96-bit reductions of the MDS layers, in ALU-only form
 #endif
@@ -51,6 +54,12 @@ __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
     u64 x3 = gl::mul_alu(x, x2);
     u64 x4 = gl::sqr_alu(x2);
     return gl::mad_alu(x3, x4, c);
+#elif defined(GLB_POSEIDON_SQR3) && GLB_POSEIDON_SQR3
+    // A/B: squarings with three 32 x 32 products (gl::sqr3); 2: only the first of the two
+    u64 x2 = gl::sqr3(x);
+    u64 x3 = gl::mul(x, x2);
+    u64 x4 = GLB_POSEIDON_SQR3 == 2 ? gl::sqr(x2) : gl::sqr3(x2);
+    return gl::mad(x3, x4, c);
 #else
     u64 x2 = gl::sqr(x);
     u64 x3 = gl::mul(x, x2);

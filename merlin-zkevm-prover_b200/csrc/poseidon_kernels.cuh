@@ -206,6 +206,37 @@ __global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_tree_level(u64
     o[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
 }
 
+// The last levels of a tree in ONE launch: a single CTA walks the levels from `pending` <= 2 * kThreads nodes down to the root
+// (one permutation per thread per level, a CTA barrier between levels).  A level this small is bound by the latency of one
+// permutation per thread either way; fusing them removes log2(pending) - 1 launches from every tree, which is what the small FRI
+// layer trees (friProve.cpp:120-123) and the gathered top of the multi-GPU commit consist of.
+__global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_tree_top(u64 *__restrict__ level, u64 pending)
+{
+    while (pending > 1) {
+        const u64 nparents = (pending - 1) / 2 + 1;
+        u64 *parents = level + pending * 4;
+        for (u64 idx = threadIdx.x; idx < nparents; idx += blockDim.x) {
+            u64 s[12];
+            const ulonglong2 *c = reinterpret_cast<const ulonglong2 *>(level + idx * 8);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                ulonglong2 v = c[i];
+                s[2 * i] = v.x;
+                s[2 * i + 1] = v.y;
+            }
+#pragma unroll
+            for (int i = 8; i < 12; i++) s[i] = 0;
+            permute<true>(s);
+            ulonglong2 *o = reinterpret_cast<ulonglong2 *>(parents + idx * 4);
+            o[0] = make_ulonglong2(gl::canon(s[0]), gl::canon(s[1]));
+            o[1] = make_ulonglong2(gl::canon(s[2]), gl::canon(s[3]));
+        }
+        __syncthreads();
+        level = parents;
+        pending /= 2;
+    }
+}
+
 // Derive the device tables from the generated parameter header (poseidon_constants.cuh).
 inline cudaError_t upload_constants()
 {
@@ -251,6 +282,10 @@ inline int launch_tree_levels(u64 *tree, u64 nrows, cudaStream_t st)
     int launches = 0;
     u64 pending = nrows, next_index = 0;
     while (pending > 1) {
+        if (pending <= 2 * kThreads) { // the remaining levels in one CTA
+            k_tree_top<<<1, kThreads, 0, st>>>(tree + next_index, pending);
+            return launches + 1;
+        }
         u64 next_n = (pending - 1) / 2 + 1; // reference :283-300 (power-of-two heights only are meaningful)
         k_tree_level<<<grid_for(next_n), kThreads, 0, st>>>(tree + next_index + pending * 4, tree + next_index, next_n);
         launches++;

@@ -57,6 +57,29 @@ __device__ __forceinline__ void store_3d(const CUtensorMap *map, const void *sme
                  ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
                  : "memory");
 }
+// 4-D variants (the pass output view splits the row index inside a tile into two digits, see ntt2.cuh)
+__device__ __forceinline__ void load_4d(void *smem_dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, int c2, int c3)
+{
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+__device__ __forceinline__ void store_4d(const CUtensorMap *map, const void *smem_src, int c0, int c1, int c2, int c3)
+{
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+// Ampere-style 8-byte asynchronous copy global -> shared (LDGSTS); src_bytes = 0 writes zeros instead of reading.
+__device__ __forceinline__ void cp_async_8(void *smem_dst, const void *gmem_src, uint32_t src_bytes)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+// arrive on `bar` once all cp.async issued so far by this thread have landed (the arrival is part of the barrier's expected count)
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t *bar)
+{
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // wait until at most N of this thread's committed bulk groups still READ their shared-memory source
 template <int N> __device__ __forceinline__ void store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
@@ -98,6 +121,23 @@ inline int make_map_3d(CUtensorMap *map, const void *base, uint64_t pitch, uint6
     // 64-bit words travel as pairs of 32-bit lanes for the copy engine: there is no 8-byte unsigned type in every driver, and
     // a plain copy does not care -- use UINT64 where available.
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
+// Output view of a non-last pass tile: the position index k inside a tile of R = 16 * R2 rows is written k = k1 + 16 * k2, so the
+// matrix row ((hi * R + k) << log_rest) + low is seen as [k2 + R2 * hi][k1][low][col]:
+//     dims (ncols, 2^log_rest, 16, nrows >> (log_rest + 4)),   box = (box_cols, 1, 1, R2):
+// the R2 outputs of one first-stage frequency k1, which a thread group holds in R2 consecutive shared-memory rows.
+inline int make_map_4d(CUtensorMap *map, const void *base, uint64_t pitch, uint64_t ncols, uint64_t nrows, uint32_t log_rest, uint32_t box_cols, uint32_t r2)
+{
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return -1;
+    const cuuint64_t dims[4] = {ncols, 1ULL << log_rest, 16, nrows >> (log_rest + 4)};
+    const cuuint64_t strides[3] = {pitch * 8, (pitch * 8) << log_rest, (pitch * 8) << (log_rest + 4)};
+    const cuuint32_t box[4] = {box_cols, 1, 1, r2};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 4, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? 0 : (int)r;
 }

@@ -171,6 +171,50 @@ static void test_batch_and_avx512_entry_points()
     for (int k = 0; k < 4; k++) { EXPECT_EQ(Goldilocks::toU64(d2[k]), Goldilocks::toU64(da[k])); EXPECT_EQ(Goldilocks::toU64(d2[4 + k]), Goldilocks::toU64(db[k])); }
 }
 
+// The literal stage-1 sequence of Starks::genProof (starks.cpp:52-59) with the resident stage switched on: extendPol keeps the
+// extended matrix and the tree it hashed during the download on the device, merkelize() only fetches the nodes, and the queries
+// (friProve.cpp:219-250) can be served from the device copies.  Everything must equal the non-resident path.
+static void test_resident_stage()
+{
+    const uint64_t N = 1 << 10, NE = 1 << 11, ncols = 20;
+    std::vector<Goldilocks::Element> in(N * ncols), out(NE * ncols), out2(NE * ncols);
+    for (uint64_t i = 0; i < N * ncols; i++) in[i] = Goldilocks::fromU64((0x9E3779B97F4A7C15ULL * (i + 12345)) % P);
+    NTT_Goldilocks ntt(N);
+    EXPECT_EQ((uint64_t)gl_set_resident(1), 0);
+    ntt.extendPol(out.data(), in.data(), NE, N, ncols);
+    uint64_t *dl = nullptr, *dt = nullptr;
+    EXPECT_EQ((uint64_t)gl_resident_query((const uint64_t *)out.data(), ncols, NE, &dl, &dt), 0);
+    MerkleTreeGL tree(NE, ncols, out.data());
+    tree.merkelize(); // served from the resident tree
+    // queries from the device copies, all in one call
+    const uint64_t idx[5] = {0, 1, 777, NE / 2, NE - 1};
+    const uint64_t psize = ncols + tree.MerkleProofSize() * HASH_SIZE;
+    std::vector<Goldilocks::Element> proofs(5 * psize), one(psize);
+    EXPECT_EQ((uint64_t)gl_group_proofs_dev((uint64_t *)proofs.data(), dl, dt, NE, ncols, idx, 5), 0);
+    for (int q = 0; q < 5; q++) {
+        tree.getGroupProof(one.data(), idx[q]);
+        for (uint64_t k = 0; k < psize; k++) EXPECT_EQ(Goldilocks::toU64(proofs[q * psize + k]), Goldilocks::toU64(one[k]));
+    }
+    // the same without the resident stage
+    EXPECT_EQ((uint64_t)gl_set_resident(0), 0);
+    EXPECT_EQ((uint64_t)(gl_resident_query((const uint64_t *)out.data(), ncols, NE, &dl, &dt) != 0), 1);
+    ntt.extendPol(out2.data(), in.data(), NE, N, ncols);
+    for (uint64_t i = 0; i < NE * ncols; i++) EXPECT_EQ(Goldilocks::toU64(out[i]), Goldilocks::toU64(out2[i]));
+    MerkleTreeGL tree2(NE, ncols, out2.data());
+    tree2.merkelize();
+    for (uint64_t i = 0; i < tree.getTreeNumElements(); i++) EXPECT_EQ(Goldilocks::toU64(tree.nodes[i]), Goldilocks::toU64(tree2.nodes[i]));
+    // a host buffer that changed after extendPol must not be served from the stale device copy: resident on, overwrite, merkelize
+    EXPECT_EQ((uint64_t)gl_set_resident(1), 0);
+    ntt.extendPol(out.data(), in.data(), NE, N, ncols);
+    for (uint64_t i = 0; i < NE * ncols; i++) out[i] = Goldilocks::fromU64(Goldilocks::toU64(out[i]) ^ 1);
+    MerkleTreeGL tree3(NE, ncols, out.data());
+    tree3.merkelize();
+    std::vector<Goldilocks::Element> nodes(tree3.getTreeNumElements());
+    PoseidonGoldilocks::merkletree_seq(nodes.data(), out.data(), ncols, NE);
+    for (int k = 0; k < 4; k++) EXPECT_EQ(Goldilocks::toU64(tree3.nodes[nodes.size() - 4 + k]), Goldilocks::toU64(nodes[nodes.size() - 4 + k]));
+    gl_set_resident(0);
+}
+
 int main()
 {
     try
@@ -180,6 +224,7 @@ int main()
         test_extendPol_and_stage_commit();
         test_concurrent_callers();
         test_batch_and_avx512_entry_points();
+        test_resident_stage();
     }
     catch (const std::exception &e)
     {

@@ -1,7 +1,7 @@
 """Worker of the multi-rank tests (launched with torch.distributed.run by test_shard_plan.py / test_gpu_mgpu.py).
 
   mode "gloo": CPU only.  Every rank runs the ORACLE on its column block, the exchange goes through
-               torch.distributed (gloo send/recv), the shard plan (merlin-zkevm-prover_b200/shard_plan.py)
+               torch.distributed (gloo send/recv), the shard plan (tests/shard_plan.py)
                assembles the tree; checked against the single-process oracle.  Tests the host-side logic.
   mode "nccl": one GPU per rank.  gl_commit_mgpu / gl_mgpu_gather_tree through the C ABI, checked against the oracle.
 """
@@ -34,12 +34,47 @@ def top_levels(o, tree, n_ext, first_level, sp):
     return tree
 
 
+# root of the c2 stage commit (2^23 x 600 -> 2^24, gl_fill_synthetic seed 1): pinned on one GPU by
+# tests/test_gpu_fullsize.py::test_c2_lde_sampled_columns_and_tree_paths (sampled LDE columns against the reference, sampled
+# authentication paths re-hashed on the CPU up to this root)
+C2_ROOT = [0xF68B21F12F746043, 0x1173C26EB33074DB, 0x5D94C8FA42CEBCC0, 0x2C3189EE0E59DD6B]
+
+
+def full_size_check(glb, o, rank, world):
+    """BASELINE configs[2]: the c2 commit sharded over `world` GPUs.  Every word of this rank's first 8 LDE columns against the CPU
+    reference run on exactly those columns, this rank's received row panels against its own LDE columns of the same rows, and the
+    root against the single-GPU one."""
+    logn, loge, ncols = 23, 24, 600
+    n, e = 1 << logn, 1 << loge
+    L = glb.lib()
+    c0, c1 = int(L.gl_mgpu_col_start(ncols, world, rank)), int(L.gl_mgpu_col_start(ncols, world, rank + 1))
+    w, rows = c1 - c0, e // world
+    din = glb.DeviceBuffer(n * w)
+    dlde = glb.DeviceBuffer(e * w)
+    dpan = glb.DeviceBuffer(rows * ncols)
+    dsub = glb.DeviceBuffer(glb.tree_num_elements(rows))
+    glb.fill_synthetic_cols_dev(din.ptr, n, c0, w, ncols, 1)
+    root = glb.commit_mgpu(dlde.ptr, dpan.ptr, dsub.ptr, din.ptr, e, n, ncols)
+    assert [int(v) for v in root] == C2_ROOT, "c2 root on %d GPUs: %s" % (world, " ".join("%016X" % int(v) for v in root))
+    k = min(8, w)
+    got = glb.download_cols(dlde.ptr, e, w, 0, k)
+    cpu = pyoracle.ref() or o
+    x = np.ascontiguousarray(glb.synthetic_host_cols(n, ncols, np.arange(c0, c0 + k), 1))
+    assert np.array_equal(got, cpu.extend_pol(x, e)), "c2 LDE columns of rank %d" % rank
+    # my rows of my own columns came back through the exchange unchanged (panel `rank`)
+    off = rows * c0
+    pan = dpan.download(rows * w, off).reshape(rows, w)
+    mine = glb.download_cols(dlde.ptr + 8 * (rank * rows * w), rows, w, 0, w)
+    assert np.array_equal(pan, mine), "row panel of rank %d" % rank
+
+
 def main():
     mode = sys.argv[1]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     glb = ge.load()
-    sp = __import__("importlib").import_module("merlin_zkevm_prover_b200.shard_plan")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import shard_plan as sp
     o = pyoracle.oracle()
     if mode == "gloo":
         dist.init_process_group("gloo")
@@ -116,6 +151,9 @@ def main():
             assert np.array_equal(root2, tree_full[-4:]), "host-pointer root differs (%d,%d,%d)" % (n, e, ncols)
             assert np.array_equal(hpan[:rows * ncols], pan), "host-pointer panels differ"
             assert np.array_equal(hsub, sub_dev), "host-pointer subtree differs"
+        dist.barrier()
+    if mode == "nccl" and os.environ.get("GLB_MGPU_FULL") == "1":
+        full_size_check(glb, o, rank, world)
         dist.barrier()
     if mode == "nccl":
         glb.mgpu_shutdown()

@@ -1,4 +1,5 @@
-"""Host-side sharding plan of the multi-GPU commit -- pure index arithmetic, no device code.
+"""TEST SUPPORT (not part of the product package): the host-side sharding plan of the multi-GPU commit restated as
+pure index arithmetic, no device code.
 
 The same formulas are implemented in csrc/glb200.cu (col_start, level_offset, the panel layout of
 gl_commit_mgpu); tests/test_shard_plan.py checks them on CPU with a world_size-2 gloo group by running

@@ -33,6 +33,11 @@ def test_field_ops(glb):
         "add_c": [(x + y) % P for x, y in zip(ai, bi)],
         "sqr": [(x * x) % P for x in ai],
         "canon": [x % P for x in ai],
+        # the IMAD.WIDE-free butterfly forms of the NTT passes (gl64.cuh canon_sel / add_cx / sub_cx)
+        "add_cx": [(x + y) % P for x, y in zip(ai, bi)],
+        "sub_cx": [(x - y) % P for x, y in zip(ai, bi)],
+        "canon_sel": [x % P for x in ai],
+        "sqr3": [(x * x) % P for x in ai],
     }
     for op, w in want.items():
         got = glb.field_op_host(op, a, b, c)
