@@ -42,8 +42,14 @@ WORKLOADS = {
     "mid": (20, 21, 256),    # profiling shape: row pitch 2 KiB, fits ncu kernel replay
 }
 SEED = 1
-# ncu capture of the shipped leaf kernel (per-opcode warp-instruction counts from the source page)
-INSTR_PER_PERM, TRAFFIC_RATIO, INSTR_SOURCE = 13617.0, 1.003, "profiles/r1_24_leaf_ncu_split_circulant.txt minus 216 (static SASS delta of the second CRT level)"
+# ncu capture of the shipped leaf kernel: per-opcode warp-instruction counts per permutation from the source page, and its DRAM traffic
+def leaf_mix():
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_leaf_instr_mix.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {"source": "fallback: profiles/r2_12_leaf_ncu_shipped.txt", "warp_instr_per_perm": 13912.0, "imad_wide": 2609.0, "imad_other": 1726.0,
+                "fp64": 3802.0, "alu": 4827.0, "i2f": 500.0, "dram_bytes_per_algorithmic_byte": 1.003}
 
 
 def peaks():
@@ -107,6 +113,50 @@ def permutations(loge, ncols):
     e = 1 << loge
     leaf = e * ((ncols + 7) // 8) if ncols > 4 else 0
     return leaf, e - 1
+
+
+def leaf_roofline(glb, leaf_perm, leaf_ms, leaf_share, leaf_bytes, clocks, hbm_peak, peak_src, kernel_name="poseidon::k_linear_hash_rows"):
+    """Roofline object of the leaf-hashing kernel on ONE GPU (leaf_perm permutations in leaf_ms)."""
+    pk = glb.measure_issue_peaks()
+    mix = leaf_mix()
+    perm_rate = leaf_perm / (leaf_ms / 1e3)
+    sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+    nsmsp = 148 * 4
+    # (1) issue slots: one warp instruction per clock per SM sub-partition is the hardware ceiling
+    warp_instr_rate = perm_rate / 32 * mix["warp_instr_per_perm"]
+    issue_peak = nsmsp * sm_hz
+    # (2) pipe model (DESIGN.md 4.0; profiles/r2_01_ubench_pipes.txt): an IMAD.WIDE holds the sub-partition for c_w clocks and nothing
+    # issues beside it; the other IMAD forms + FP64, the ALU-pipe instructions and the conversions run on three pipes side by side.
+    # The per-instruction costs are measured NOW by gl_measure_issue_peaks (chains of real IMAD.WIDE.U32 / 3-input IADD3 / DFMA).
+    c_w = nsmsp * sm_hz * 32 / pk["imad_wide_lane_ops_per_s"]
+    c_a = nsmsp * sm_hz * 32 / pk["iadd3_lane_ops_per_s"]
+    c_d = nsmsp * sm_hz * 32 / pk["dfma_lane_ops_per_s"]
+    t_model = c_w * mix["imad_wide"] + max(c_a * mix["imad_other"] + c_d * mix["fp64"], c_a * mix["alu"], 4 * c_a * mix["i2f"])
+    pipe_bound = nsmsp * sm_hz / t_model * 32          # permutations per second if the pipes were never idle
+    # (3) SURVEY 8(d) accounting of the REFERENCE algorithm: 1144 modular multiplications x 5 IMAD.WIDE-class + 1008 small-constant
+    # MACs x 2 per permutation, against the measured real IMAD.WIDE.U32 rate (our dense / paired form needs fewer real multiplies)
+    imad_algo = perm_rate * (1144 * 5 + 1008 * 2)
+    roofline = {"kernel": "%s (leaf hashing, %.0f%% of the step)" % (kernel_name, 100 * leaf_share),
+                "bound": "issue", "achieved": warp_instr_rate / 1e12, "peak": issue_peak / 1e12, "unit": "T warp-instr/s",
+                "frac": warp_instr_rate / issue_peak,
+                "peak_source": "148 SMs x 4 sub-partitions x %.0f MHz (SM clock sampled by nvidia-smi during the timed region): one warp instruction per clock per sub-partition" % (sm_hz / 1e6),
+                "instr_per_permutation": mix["warp_instr_per_perm"], "instr_source": mix["source"],
+                "Gperm_per_s": perm_rate / 1e9,
+                "pipe_model": {"clk_per_imad_wide": c_w, "clk_per_alu_or_imad": c_a, "clk_per_dfma": c_d,
+                               "measured_by": "gl_measure_issue_peaks() in this run: IMAD.WIDE.U32 %.2f, IADD3 %.2f, DFMA %.2f T lane-ops/s"
+                                              % (pk["imad_wide_lane_ops_per_s"] / 1e12, pk["iadd3_lane_ops_per_s"] / 1e12, pk["dfma_lane_ops_per_s"] / 1e12),
+                               "per_permutation": {k: mix[k] for k in ("imad_wide", "imad_other", "fp64", "alu", "i2f")},
+                               "clk_per_warp_permutation_model": t_model, "clk_per_warp_permutation_measured": nsmsp * sm_hz * 32 / perm_rate,
+                               "bound_Gperm_per_s": pipe_bound / 1e9, "frac_of_pipe_bound": perm_rate / pipe_bound,
+                               "formula": "T = c_w*WIDE + max(c_a*IMADother + c_d*FP64, c_a*ALU, 4*c_a*I2F) clocks per warp permutation"},
+                "imad": {"achieved_lane_ops_per_s": imad_algo, "peak_lane_ops_per_s": pk["imad_wide_lane_ops_per_s"], "frac": imad_algo / pk["imad_wide_lane_ops_per_s"],
+                         "note": "SURVEY 8(d) accounting of the reference algorithm (1144 modmul x 5 + 1008 MAC x 2 IMAD-class lane-ops per permutation) against the measured real "
+                                 "IMAD.WIDE.U32 rate; above 1 because the dense-form kernel executes 2609 IMAD.WIDE per permutation, not 5720"},
+                "hbm": {"achieved": leaf_bytes / (leaf_ms / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": leaf_bytes / (leaf_ms / 1e3) / 1e9 / hbm_peak,
+                        "peak_source": peak_src},
+                "traffic": leaf_bytes * mix["dram_bytes_per_algorithmic_byte"],
+                "traffic_source": "dram__bytes_read+write of the same kernel, ncu --set full on the 2^21 x 256 shape (%s), scaled by bytes" % mix["source"]}
+    return roofline
 
 
 # --------------------------------------------------------------------------------------- CPU arm
@@ -285,28 +335,7 @@ def main():
     leaf_perm, tree_perm = permutations(loge, ncols)
     leaf_bytes = e * ncols * 8 + e * 32                 # read the extended matrix once, write the digests
     lde_bytes, lde_passes = lde_pass_bytes(logn, loge, ncols)
-    pk = glb.measure_issue_peaks()
-    perm_rate = leaf_perm / (phase["leaf_ms"] / 1e3)
-    # warp instructions per permutation of the shipped k_linear_hash_rows: ncu source page, see INSTR_SOURCE
-    warp_instr_rate = perm_rate / 32 * INSTR_PER_PERM
-    issue_peak = pk["iadd3_lane_ops_per_s"] / 32        # one warp instruction per clock per SM sub-partition, measured
-    # SURVEY 8(d) accounting of the REFERENCE algorithm: 1144 modular multiplications x 5 IMAD.WIDE-class + 1008 small-constant
-    # MACs x 2 per permutation; our dense / paired form needs fewer real multiplies, so this credits the algorithmic saving
-    imad_algo = perm_rate * (1144 * 5 + 1008 * 2)
-    roofline = {"kernel": "poseidon::k_linear_hash_rows (leaf hashing, %.0f%% of the step)" % (100 * phase["leaf_ms"] / dev_ms),
-                "bound": "issue", "achieved": warp_instr_rate / 1e12, "peak": issue_peak / 1e12, "unit": "T warp-instr/s",
-                "frac": warp_instr_rate / issue_peak,
-                "peak_source": "gl_measure_issue_peaks() in this run: IADD3 chain = %.3f T warp-instr/s (148 SMs x 4 sub-partitions x SM clock); "
-                               "IMAD.WIDE.U32 %.2f T lane-ops/s, DFMA %.2f T lane-ops/s" % (issue_peak / 1e12, pk["imad_wide_lane_ops_per_s"] / 1e12, pk["dfma_lane_ops_per_s"] / 1e12),
-                "instr_per_permutation": INSTR_PER_PERM, "instr_source": INSTR_SOURCE,
-                "Gperm_per_s": perm_rate / 1e9,
-                "imad": {"achieved_lane_ops_per_s": imad_algo, "peak_lane_ops_per_s": pk["imad_wide_lane_ops_per_s"], "frac": imad_algo / pk["imad_wide_lane_ops_per_s"],
-                         "note": "SURVEY 8(d) accounting of the reference algorithm (1144 modmul x 5 + 1008 MAC x 2 IMAD-class lane-ops per permutation) against the measured real "
-                                 "IMAD.WIDE.U32 rate; above 1 means the dense-form kernel executes fewer multiplies than that accounting assumes"},
-                "hbm": {"achieved": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": leaf_bytes / (phase["leaf_ms"] / 1e3) / 1e9 / hbm_peak,
-                        "peak_source": peak_src},
-                "traffic": leaf_bytes * TRAFFIC_RATIO,
-                "traffic_source": "dram__bytes_read+write of the same kernel, ncu --set full on the 2^21 x 256 shape (%s), scaled by bytes" % INSTR_SOURCE}
+    roofline = leaf_roofline(glb, leaf_perm, phase["leaf_ms"], phase["leaf_ms"] / dev_ms, leaf_bytes, clocks, hbm_peak, peak_src)
     epasses = (n * (1 if logn <= 8 else (logn + 7) // 8) + e * (1 if loge <= 8 else (loge + 7) // 8)) * ncols
     lde_algo = (n + e) * ncols * 8
     phases = {

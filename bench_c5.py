@@ -91,6 +91,8 @@ def run(args, glb, config, peaks, ClockSampler, seed=1):
     dev_ms = sum(v.get("lde_ms", 0) + v.get("leaf_ms", 0) + v.get("tree_ms", 0) for v in last.values()) + last["fri"]["wall_ms"]
     leaf_ms = sum(v.get("leaf_ms", 0) for v in last.values())
     leaf_bytes = e * 8 * (sum(c for _, c in STAGES) + QDIM * QDEG) + 4 * e * 32
+    from bench import leaf_roofline
+    leaf_perms = e * (sum((c + 7) // 8 for _, c in STAGES) + (QDIM * QDEG + 7) // 8)
     config = dict(config)
     config["workload"] = "c5: full commit sequence of one synthetic batch proof: stage-1/2/3 (600/48/96 cols) + Q (3 x qDeg 2) + FRI layers %s, 2^23 -> 2^24" % FRI_STEPS
     config["ncols"] = sum(c for _, c in STAGES) + QDIM * QDEG
@@ -99,10 +101,8 @@ def run(args, glb, config, peaks, ClockSampler, seed=1):
             "dtype": "u64 (Goldilocks field, integer pipe)", "data": "synthetic (splitmix64 of the element index mod p, generated in HBM)",
             "config": config, "roots": [" ".join("%016X" % int(v) for v in r) for r in roots], "clocks": clocks, "e2e": None,
             "gpu_launches": launches,
-            "roofline": {"kernel": "poseidon::k_linear_hash_rows (leaf hashing of the 4 stage trees, %.0f%% of the sequence)" % (100 * leaf_ms / dev_ms),
-                         "bound": "hbm", "achieved": leaf_bytes / (leaf_ms / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": leaf_bytes / (leaf_ms / 1e3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
-                         "note": "integer-issue bound, see DESIGN.md 4.2"},
+            "roofline": leaf_roofline(glb, leaf_perms, leaf_ms, leaf_ms / dev_ms, leaf_bytes, clocks, hbm_peak, peak_src,
+                                      "poseidon::k_linear_hash_rows over the 4 stage trees"),
             "phases": last, "cpu_baseline": None}
     print(json.dumps(line))
     return 0

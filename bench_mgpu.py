@@ -13,7 +13,7 @@ import numpy as np
 
 def run(args, glb, dist, rank, world, local_rank, config, workloads):
     import torch
-    from bench import ClockSampler, SEED, peaks, permutations
+    from bench import ClockSampler, SEED, leaf_roofline, peaks, permutations
     logn, loge, ncols = workloads[args.workload]
     n, e = 1 << logn, 1 << loge
     dev = torch.device("cuda", local_rank)
@@ -100,6 +100,7 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
     glb.mgpu_shutdown()
     if rank != 0:
         return 0
+    # (rank 0 measures the issue-rate probes for the roofline after the communicator is gone)
     dev_ms, lde_ms, ex_ms, leaf_ms, tree_ms = [float(x) for x in tt.tolist()]
     hbm_peak, peak_src = peaks()
     leaf_perm, tree_perm = permutations(loge, ncols)
@@ -112,10 +113,8 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
             "vs_baseline": None, "dtype": "u64 (Goldilocks field, integer pipe)", "data": "synthetic (splitmix64 of the element index mod p, generated in HBM)",
             "config": config, "root": " ".join("%016X" % int(v) for v in root), "roots_agree": same_root, "clocks": clocks, "e2e": e2e,
             "gpu_launches": int(ln.item()),
-            "roofline": {"kernel": "poseidon::k_linear_hash_rows<panels> (leaf hashing, %.0f%% of the step)" % (100 * leaf_ms / dev_ms), "bound": "hbm",
-                         "achieved": leaf_bytes / (leaf_ms / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": leaf_bytes / (leaf_ms / 1e3) / 1e9 / hbm_peak,
-                         "traffic": None, "peak_source": peak_src,
-                         "note": "integer-pipe bound: %.3f G Poseidon permutations/s per GPU" % (leaf_perm / world / leaf_ms / 1e6)},
+            "roofline": leaf_roofline(glb, leaf_perm // world, leaf_ms, leaf_ms / dev_ms, leaf_bytes, clocks, hbm_peak, peak_src,
+                                      "poseidon::k_linear_hash_rows<panels>, per GPU"),
             "phases": {"lde": {"ms": lde_ms},
                        "exchange": {"ms": ex_ms, "bytes_sent_per_rank": (world - 1) * rows * w * 8, "row_chunks": chunks,
                                     "note": "exposed part only: the rows are exchanged in %d chunks on a second stream and chunk j+1 moves while chunk j is hashed" % chunks,

@@ -49,6 +49,13 @@ int fail(int code, const char *fmt, ...)
                         cudaGetErrorString(e__), __FILE__, __LINE__);                              \
     } while (0)
 
+// inside the copy / compute pipelines: remember the first failing call (the loop condition stops on it; clean-up follows the loop)
+#define CUP(call)                                                                                          \
+    do {                                                                                                   \
+        cudaError_t e__ = (call);                                                                          \
+        if (e__ != cudaSuccess && rc == GL_OK) rc = fail(GL_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
 #define TRY(call)                   \
     do {                            \
         int rc__ = (call);          \
@@ -79,6 +86,8 @@ struct Ctx {
     int ntt_variant = 0;        // 0: k_pass (direct loads, two CTAs per SM alternate load and butterfly phases -- the faster one),
                                 // 2 / 3: k_pass2 (ntt2.cuh: TMA / cp.async ring of 2 / 3 tile buffers); env GLB_NTT or gl_set_ntt_variant
     int sms = 148;
+    void *small_dev = nullptr;  // 1 MiB device staging of the small host-pointer transforms (no cudaMalloc per call: FRIProve's fold calls
+                                // INTT on nX x 3 matrices from an OpenMP loop, friProve.cpp:44-107)
     u64 *qbuf = nullptr;        // grow-only staging of the batched query calls: [indices | gathered words] (device)
     size_t qbuf_words = 0;
     std::mutex mu;
@@ -741,20 +750,20 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
             const u64 c0 = starts[k];
             const u32 w = (u32)(starts[k + 1] - c0);
             u64 *st = (u64 *)stage.p + (k & 1) * (size_t)n * cb;
-            if (k >= 2) cudaStreamWaitEvent(g.s_h2d, ev_done[k - 2], 0); // staging buffer free again
-            cudaMemcpy2DAsync(st, cb * 8, in + c0, ncols * 8, (size_t)w * 8, n, cudaMemcpyHostToDevice, g.s_h2d);
-            cudaEventRecord(ev_in[k], g.s_h2d);
-            cudaStreamWaitEvent(g.stream, ev_in[k], 0);
-            rc = run_ntt(coef, cp, st, cb, tmp, cp, logn, w, true, 2, n);
+            if (k >= 2) CUP(cudaStreamWaitEvent(g.s_h2d, ev_done[k - 2], 0)); // staging buffer free again
+            CUP(cudaMemcpy2DAsync(st, cb * 8, in + c0, ncols * 8, (size_t)w * 8, n, cudaMemcpyHostToDevice, g.s_h2d));
+            CUP(cudaEventRecord(ev_in[k], g.s_h2d));
+            CUP(cudaStreamWaitEvent(g.stream, ev_in[k], 0));
+            if (rc == GL_OK) rc = run_ntt(coef, cp, st, cb, tmp, cp, logn, w, true, 2, n);
             if (rc == GL_OK) rc = run_ntt(lde + c0, ncols, coef, cp, tmp, cp, loge, w, false, 0, n);
-            cudaEventRecord(ev_done[k], g.stream);
+            CUP(cudaEventRecord(ev_done[k], g.stream));
             if (do_tree && ncols > 4 && rc == GL_OK) { // hash this block's columns now; the capacity words wait in the leaf slots
                 poseidon::k_linear_hash_partial<<<poseidon::grid_for(n_ext), poseidon::kThreads, 0, g.stream>>>((u64 *)t.p, lde, n_ext, ncols, (u32)c0, w);
                 g.launches++;
             }
             if (lde_out) {
-                cudaStreamWaitEvent(g.s_d2h, ev_done[k], 0);
-                cudaMemcpy2DAsync(lde_out + c0, ncols * 8, lde + c0, ncols * 8, (size_t)w * 8, n_ext, cudaMemcpyDeviceToHost, g.s_d2h);
+                CUP(cudaStreamWaitEvent(g.s_d2h, ev_done[k], 0));
+                CUP(cudaMemcpy2DAsync(lde_out + c0, ncols * 8, lde + c0, ncols * 8, (size_t)w * 8, n_ext, cudaMemcpyDeviceToHost, g.s_d2h));
             }
         }
         cudaError_t e = cudaGetLastError();
@@ -863,6 +872,8 @@ void gl_shutdown(void)
     if (g.roots) cudaFree(g.roots);
     if (g.rscale) cudaFree(g.rscale);
     resident_drop();
+    if (g.small_dev) cudaFree(g.small_dev);
+    g.small_dev = nullptr;
     if (g.qbuf) cudaFree(g.qbuf);
     g.qbuf = nullptr;
     g.qbuf_words = 0;
@@ -1156,6 +1167,15 @@ int gl_ntt_host(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncol
     API_ENTER();
     if (!dst) dst = (uint64_t *)src;
     size_t bytes = (size_t)size * ncols * 8;
+    constexpr size_t kSmall = (size_t)1 << 20;
+    if (bytes <= kSmall) { // persistent staging: H2D, one or two launches, D2H on the library stream, one synchronisation
+        if (!g.small_dev) CU(cudaMalloc(&g.small_dev, kSmall));
+        CU(cudaMemcpyAsync(g.small_dev, src, bytes, cudaMemcpyHostToDevice, g.stream));
+        TRY(ntt_dev((u64 *)g.small_dev, (const u64 *)g.small_dev, size, ncols, inverse, extend));
+        CU(cudaMemcpyAsync(dst, g.small_dev, bytes, cudaMemcpyDeviceToHost, g.stream));
+        CU(cudaStreamSynchronize(g.stream));
+        return GL_OK;
+    }
     DevBuf d;
     TRY(d.alloc(bytes));
     TRY(gl_h2d(d.p, src, bytes));
@@ -1457,13 +1477,13 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
             const u64 c0 = k * cb;
             const u32 ww = (u32)((w - c0 < cb) ? w - c0 : cb);
             u64 *st = (u64 *)stage.p + (k & 1) * (size_t)n * cb;
-            if (k >= 2) cudaStreamWaitEvent(g.s_h2d, ev_done[k - 2], 0); // staging buffer free again
-            cudaMemcpy2DAsync(st, cb * 8, in_cols_host + c0, w * 8, (size_t)ww * 8, n, cudaMemcpyHostToDevice, g.s_h2d);
-            cudaEventRecord(ev_in[k], g.s_h2d);
-            cudaStreamWaitEvent(g.stream, ev_in[k], 0);
-            rc = run_ntt(coef, cp, st, cb, tmp, cp, logn, ww, true, 2, n);
+            if (k >= 2) CUP(cudaStreamWaitEvent(g.s_h2d, ev_done[k - 2], 0)); // staging buffer free again
+            CUP(cudaMemcpy2DAsync(st, cb * 8, in_cols_host + c0, w * 8, (size_t)ww * 8, n, cudaMemcpyHostToDevice, g.s_h2d));
+            CUP(cudaEventRecord(ev_in[k], g.s_h2d));
+            CUP(cudaStreamWaitEvent(g.stream, ev_in[k], 0));
+            if (rc == GL_OK) rc = run_ntt(coef, cp, st, cb, tmp, cp, logn, ww, true, 2, n);
             if (rc == GL_OK) rc = run_ntt((u64 *)lde_cols + c0, w, coef, cp, tmp, cp, loge, ww, false, 0, n);
-            cudaEventRecord(ev_done[k], g.stream);
+            CUP(cudaEventRecord(ev_done[k], g.stream));
         }
         cudaError_t e = cudaGetLastError();
         for (u64 k = 0; k < nb; k++) { cudaEventDestroy(ev_in[k]); cudaEventDestroy(ev_done[k]); } // released when complete

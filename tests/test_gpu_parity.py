@@ -352,6 +352,51 @@ def test_fri_layer_commit(glb, oracle, fixtures):
 
 
 @pytest.mark.gpu
+def test_fri_fold_literal_shim_path(glb, oracle):
+    """FRIProve::prove's fold loop as the reference writes it (friProve.cpp:36-107): per group an NTT_Goldilocks(nX, 1).INTT on
+    an nX x 3 matrix -- here through gl_ntt_host, which is what the shim's INTT calls -- then polMulAxi (:192-200) and evalPol
+    (:201-217).  2^14 -> 2^10.  Must equal the oracle's restatement and the fused device kernel (gl_fri_fold_dev)."""
+    import ctypes as C
+    rng = np.random.default_rng(33)
+    pb, nb = 14, 10
+    pol = rng.integers(0, P, size=(1 << pb, 3), dtype=np.uint64)
+    x = rng.integers(0, P, size=3, dtype=np.uint64)
+    shift_inv = int(rng.integers(1, P, dtype=np.uint64))
+    pol2n, nx = 1 << nb, 1 << (pb - nb)
+    L = oracle.L
+    wi = L.glo_inv(L.glo_root_of_unity(pb))
+
+    def gl3_mul(a, b):
+        r = np.zeros(3, dtype=np.uint64)
+        L.glo_gl3_mul(r.ctypes.data_as(C.POINTER(C.c_uint64)), np.ascontiguousarray(a).ctypes.data_as(C.POINTER(C.c_uint64)),
+                      np.ascontiguousarray(b).ctypes.data_as(C.POINTER(C.c_uint64)))
+        return r
+
+    out = np.zeros((pol2n, 3), dtype=np.uint64)
+    sinv = shift_inv
+    for g in range(pol2n):
+        ppar = np.ascontiguousarray(pol[g::pol2n])                      # rows i * pol2N + g, i < nX
+        c = glb.ntt_host(ppar, inverse=True)                            # the shim's NTT_Goldilocks(nX, 1).INTT
+        r = 1
+        for i in range(nx):                                             # polMulAxi
+            c[i] = [L.glo_mul(int(v), r) for v in c[i]]
+            r = L.glo_mul(r, sinv)
+        res = c[nx - 1].copy()
+        for i in range(nx - 2, -1, -1):                                 # evalPol (Horner in F_p^3)
+            res = gl3_mul(res, x)
+            res = np.array([L.glo_add(int(res[d]), int(c[i][d])) for d in range(3)], dtype=np.uint64)
+        out[g] = res
+        sinv = L.glo_mul(sinv, wi)
+    want = oracle.fri_fold(pol, nb, shift_inv, x)
+    assert np.array_equal(out, want)
+    dpol = glb.DeviceBuffer(pol.size).upload(pol)
+    dout = glb.DeviceBuffer(pol2n * 3)
+    assert glb.lib().gl_fri_fold_dev(C.c_void_p(dout.ptr), C.c_void_p(dpol.ptr), pb, nb, shift_inv, x.ctypes.data_as(C.POINTER(C.c_uint64))) == 0
+    glb.lib().gl_sync()
+    assert np.array_equal(dout.download().reshape(-1, 3), want)
+
+
+@pytest.mark.gpu
 def test_consttree_image(glb, oracle):
     """bctree (build_const_tree.cpp:333-407): [nPols, nExt, extended constants, nodes] re-opened as MerkleTreeGL."""
     rng = np.random.default_rng(23)
