@@ -58,6 +58,9 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
     dev_ms = sum(phase.values()) / args.steps
     # max over ranks of the device time, and of every phase
     tt = torch.tensor([dev_ms] + [phase[k] / args.steps for k in ("lde_ms", "exchange_ms", "leaf_ms", "tree_ms")], dtype=torch.float64, device=dev)
+    per_rank = [torch.zeros_like(tt) for _ in range(world)]
+    dist.all_gather(per_rank, tt.clone())
+    per_rank = [[round(float(v), 3) for v in t.tolist()] for t in per_rank]   # [step, lde, exchange, leaf, tree] ms of every rank
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     ln = torch.tensor([launches], dtype=torch.int64, device=dev)
     dist.all_reduce(ln, op=dist.ReduceOp.SUM)
@@ -105,7 +108,8 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
     hbm_peak, peak_src = peaks()
     leaf_perm, tree_perm = permutations(loge, ncols)
     leaf_bytes = (e * ncols * 8 + e * 32) / world
-    chunks = 4 if (rows % 4 == 0 and rows // 4 >= 4096) else 1  # mgpu_exchange_and_hash in csrc/glb200.cu
+    chunks = 5 if (rows % 64 == 0 and rows // 64 >= 1024) else (4 if (rows % 4 == 0 and rows // 4 >= 256) else 1)  # mgpu_exchange_and_hash in csrc/glb200.cu
+    first_frac = 1 / 64 if chunks == 5 else 1 / chunks
     config = dict(config)
     config["parallelism"] = "column-split LDE x%d -> NCCL all-to-all -> row-block leaf hash + subtrees -> gathered root" % world
     line = {"metric": "commit_ext_elements_per_s", "value": e * ncols / (dev_ms / 1e3), "unit": "ext-elem/s", "n_gpus": world, "steps": args.steps,
@@ -115,10 +119,11 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
             "gpu_launches": int(ln.item()),
             "roofline": leaf_roofline(glb, leaf_perm // world, leaf_ms, leaf_ms / dev_ms, leaf_bytes, clocks, hbm_peak, peak_src,
                                       "poseidon::k_linear_hash_rows<panels>, per GPU"),
+            "ms_per_rank": {"columns": ["step", "lde", "exchange", "leaf", "tree"], "rows": per_rank},
             "phases": {"lde": {"ms": lde_ms},
                        "exchange": {"ms": ex_ms, "bytes_sent_per_rank": (world - 1) * rows * w * 8, "row_chunks": chunks,
-                                    "note": "exposed part only: the rows are exchanged in %d chunks on a second stream and chunk j+1 moves while chunk j is hashed" % chunks,
-                                    "GBps_per_rank_first_chunk": (world - 1) * rows * w * 8 / chunks / max(ex_ms, 1e-9) / 1e6},
+                                    "note": "exposed part only: the rows are exchanged in %d chunks of growing size (first %.4f of the rows) on a second stream; chunk j+1 moves while chunk j is hashed" % (chunks, first_frac),
+                                    "GBps_per_rank_first_chunk": (world - 1) * rows * w * 8 * first_frac / max(ex_ms, 1e-9) / 1e6},
                        "leaf": {"ms": leaf_ms, "permutations_per_rank": leaf_perm // world}, "tree": {"ms": tree_ms}},
             "cpu_baseline": None}
     print(json.dumps(line))

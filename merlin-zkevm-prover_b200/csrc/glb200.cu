@@ -73,6 +73,7 @@ struct Ctx {
     void *arena = nullptr;
     size_t arena_bytes = 0;
     u64 *roots = nullptr, *rscale = nullptr; // twiddle / coset-scale tables (device)
+    u64 *roots_hi = nullptr;                 // second-level twiddle table of the domains above 2^27
     u32 log_roots = 0, log_rscale = 0;
     size_t scratch_limit = (size_t)32 << 30; // upper bound; pick_col_block also stays within half of the free device memory
     std::atomic<uint64_t> launches{0};
@@ -188,21 +189,33 @@ bool is_pow2(u64 n) { return n && !(n & (n - 1)); }
 // NTT_Goldilocks object and REBUILDS it serially on every extendPol, ntt_goldilocks.cpp:328; here it is
 // built once on the device and reused); rscale[i] = 7^i / n for the most recent extend size (computeR,
 // ntt_goldilocks.hpp:153-165).
-constexpr u32 kMaxLogRoots = 27;
+// Domains above 2^27 (the reference accepts up to 2^32, ntt_goldilocks.hpp:94-97) keep only the first 2^27 powers of w_(2^L) plus a
+// second-level table of the 2^(L-27) powers w^(j 2^27); the extend scale 7^i / n is then computed on the fly instead of tabulated.
+constexpr u32 kLogRootsLo = 27;
 
 int ensure_roots(u32 logn)
 {
-    if (logn > kMaxLogRoots) return fail(GL_ERR_NOMEM, "NTT of size 2^%u needs a %llu MiB twiddle table; this build caps it at 2^%u", logn, (8ULL << logn) >> 20, kMaxLogRoots);
-    if (g.roots && g.log_roots >= logn) return GL_OK;
+    const bool big = logn > kLogRootsLo;
+    if (g.roots && (big ? g.log_roots == logn : (g.log_roots >= logn && g.log_roots <= kLogRootsLo))) return GL_OK;
     u32 L = logn < 16 ? 16 : logn;
     if (g.roots) {
         CU(cudaStreamSynchronize(g.stream));
         CU(cudaFree(g.roots));
         g.roots = nullptr;
     }
-    CU(cudaMalloc(&g.roots, (size_t)8 << L));
-    ntt::k_build_roots<<<148 * 4, 256, 0, g.stream>>>(g.roots, L);
+    if (g.roots_hi) {
+        CU(cudaFree(g.roots_hi));
+        g.roots_hi = nullptr;
+    }
+    const u64 count = 1ULL << (big ? kLogRootsLo : L);
+    CU(cudaMalloc(&g.roots, count * 8));
+    ntt::k_build_roots<<<148 * 4, 256, 0, g.stream>>>(g.roots, L, count, 0);
     g.launches++;
+    if (big) {
+        CU(cudaMalloc(&g.roots_hi, (size_t)8 << (L - kLogRootsLo)));
+        ntt::k_build_roots<<<1, 32, 0, g.stream>>>(g.roots_hi, L, 1ULL << (L - kLogRootsLo), kLogRootsLo);
+        g.launches++;
+    }
     CU(cudaGetLastError());
     g.log_roots = L;
     return GL_OK;
@@ -210,6 +223,15 @@ int ensure_roots(u32 logn)
 
 int ensure_rscale(u32 logn)
 {
+    if (logn > kLogRootsLo) { // computed on the fly by the last pass
+        if (g.rscale) {
+            CU(cudaStreamSynchronize(g.stream));
+            CU(cudaFree(g.rscale));
+        }
+        g.rscale = nullptr;
+        g.log_rscale = 0;
+        return GL_OK;
+    }
     if (g.rscale && g.log_rscale == logn) return GL_OK;
     if (g.rscale) {
         CU(cudaStreamSynchronize(g.stream));
@@ -382,6 +404,8 @@ int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpit
     p.roots = g.roots;
     p.log_roots = g.log_roots;
     p.rscale = g.rscale;
+    p.roots_hi = g.log_roots > kLogRootsLo ? g.roots_hi : nullptr;
+    p.log_lo = kLogRootsLo;
     p.cscale = scale_mode == 1 ? hpow((P + 1) / 2, logn) : 1; // 2^-logn (1: unscaled)
     const bool v2 = pass2_usable(logn, m, p.bits, tmp, tpitch, ncols);
     u32 prev = 0;
@@ -418,7 +442,7 @@ u32 pick_col_block(u64 ncols, size_t bytes_per_col)
     return (u32)cb;
 }
 // scratch pitch of a block of cb columns: whole 16-column tiles (tensor maps need an even pitch; k_pass2 reads / writes whole tiles)
-u64 pad16(u64 cb) { return (cb + 15) & ~(u64)15; }
+u64 pad16(u64 cb) { return g.ntt_variant == 0 ? cb : ((cb + 15) & ~(u64)15); }
 
 int ntt_dev(u64 *dst, const u64 *src, u64 size, u64 ncols, int inverse, int extend)
 {
@@ -848,6 +872,7 @@ int gl_init(int device)
     if (prop.major < 10) return fail(GL_ERR_CUDA, "device %s is sm_%d%d; this library is built for sm_100a only", prop.name, prop.major, prop.minor);
     g.sms = prop.multiProcessorCount;
     if (const char *v = getenv("GLB_NTT")) g.ntt_variant = atoi(v);
+    if (const char *v = getenv("GLB_SCRATCH_MIB")) g.scratch_limit = (size_t)atoll(v) << 20; // tuning runs (tools/): same as gl_set_scratch_limit
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.s_d2h, cudaStreamNonBlocking));
@@ -871,6 +896,8 @@ void gl_shutdown(void)
     g.arena_bytes = 0;
     if (g.roots) cudaFree(g.roots);
     if (g.rscale) cudaFree(g.rscale);
+    if (g.roots_hi) cudaFree(g.roots_hi);
+    g.roots_hi = nullptr;
     resident_drop();
     if (g.small_dev) cudaFree(g.small_dev);
     g.small_dev = nullptr;
@@ -1324,12 +1351,25 @@ int mgpu_exchange_and_hash(const u64 *lde_cols, u64 *row_panels, u64 *subtree, u
     rp.npanels = (u32)G;
     for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
     for (int p = 0; p < G; p++) rp.base[p] = (const u64 *)row_panels + rows * rp.start[p];
-    const u64 J = (rows % 4 == 0 && rows / 4 >= 4096) ? 4 : 1;
-    const u64 rc = rows / J;
+    // Row chunks of GROWING size: only the first chunk's transfer is exposed (the hashing of chunk j hides the transfer of chunk
+    // j+1, and hashing a row takes ~9x as long as moving it), so the first chunk is 1/64 of the rows and each next one <= 4x larger.
+    u64 bounds[8];
+    u64 J = 1;
+    bounds[0] = 0;
+    if (rows % 64 == 0 && rows / 64 >= 1024) {
+        static const u64 cum64[5] = {1, 4, 12, 32, 64}; // chunk sizes 1, 3, 8, 20, 32 sixty-fourths
+        J = 5;
+        for (u64 j = 0; j < J; j++) bounds[j + 1] = rows / 64 * cum64[j];
+    } else if (rows % 4 == 0 && rows / 4 >= 256) {
+        J = 4;
+        for (u64 j = 0; j < J; j++) bounds[j + 1] = rows / 4 * (j + 1);
+    } else {
+        bounds[1] = rows;
+    }
     CU(cudaEventRecord(g.ev[5], g.stream));
     CU(cudaStreamWaitEvent(g.s_comm, g.ev[5], 0)); // the column block is complete
     for (u64 j = 0; j < J; j++) {
-        const u64 r0 = j * rc;
+        const u64 r0 = bounds[j], rc = bounds[j + 1] - bounds[j];
         NC(nc.GroupStart());
         for (int p = 0; p < G; p++) {
             if (p == me) continue;
@@ -1597,6 +1637,7 @@ int gl_fri_fold_dev(uint64_t *out, const uint64_t *pol, uint32_t pol_bits, uint3
 {
     API_ENTER();
     if (next_bits > pol_bits || pol_bits > 32 || pol_bits - next_bits > 6) return fail(GL_ERR_ARG, "fri_fold: bits %u -> %u unsupported", pol_bits, next_bits);
+    if (pol_bits > kLogRootsLo) return fail(GL_ERR_ARG, "fri_fold: polynomials above 2^%u are not supported", kLogRootsLo);
     TRY(ensure_roots(pol_bits));
     fri::F3 xx = {x[0], x[1], x[2]};
     const u64 pol2n = 1ULL << next_bits;

@@ -129,8 +129,12 @@ struct PassParams {
     u64 nvalid;         // source rows >= nvalid are read as zeros (zero-padded LDE input)
     const u64 *roots;   // roots[i] = w_(2^log_roots)^i, i < 2^log_roots  (inter-pass twiddles)
     u32 log_roots;
-    const u64 *rscale;  // scale_mode 2: rscale[i] = 7^i / n, i < n
+    const u64 *rscale;  // scale_mode 2: rscale[i] = 7^i / n, i < n (nullptr: computed on the fly -- domains above 2^27)
     u64 cscale;         // scale_mode 1: 1/n
+    // domains above 2^27 (the reference accepts up to 2^32, ntt_goldilocks.hpp:94-97): `roots` then holds only the first 2^log_lo powers
+    // of w_(2^log_roots) and roots_hi[j] = w^(j * 2^log_lo); a twiddle is the product of one entry of each.  nullptr otherwise.
+    const u64 *roots_hi;
+    u32 log_lo;
 };
 
 template <int B2, bool CSEL = false> struct Step2 {
@@ -227,7 +231,7 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     const u64 lstep = p.dpitch << p.log_prev;
     u64 *lp = p.dst + (out_base + ((u64)k0 << p.log_prev)) * p.dpitch + col;
     auto store_all = [&](auto lmode_tag) {
-    constexpr int LMODE = decltype(lmode_tag)::value;
+    constexpr int LMODE = decltype(lmode_tag)::value; // for !LAST: 3 = two-level twiddle lookup (domains above 2^27)
     // walk the outputs in ascending kc so that the store pointer advances by compile-time multiples of dstep
     u32 kprev = 0;
 #pragma unroll
@@ -239,7 +243,9 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
         const u32 kc = B2 > 0 ? (u32)(g + 16 * k2) : (u32)j;
         u64 v = x[i];
         if (!LAST) {
-            v = gl::mul(v, p.roots[e1 * (k0 + kc)]);
+            const u32 ti = e1 * (k0 + kc);
+            if (LMODE == 3) v = gl::mul(gl::mul(v, p.roots[ti & ((1u << p.log_lo) - 1)]), p.roots_hi[ti >> p.log_lo]);
+            else v = gl::mul(v, p.roots[ti]);
             dp0 += dstep * (kc - kprev);
             kprev = kc;
             if (colok) *dp0 = v;
@@ -249,22 +255,23 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
             if (colok) *lp = gl::canon(v);
         } else {
             const u64 row = (0 - (out_base + ((u64)(k0 + kc) << p.log_prev))) & nmask;
-            v = gl::mul(v, LMODE == 1 ? p.cscale : p.rscale[row]);
+            v = gl::mul(v, LMODE == 1 ? p.cscale : (p.rscale ? p.rscale[row] : gl::mul(pow_tab(c_p7, (u32)row), c_inv2[p.logn])));
             if (colok) p.dst[row * p.dpitch + col] = gl::canon(v);
         }
     }
     };
-    if (!LAST || !p.inverse) store_all(IntTag<0>());
+    if (!LAST && p.roots_hi) store_all(IntTag<3>());
+    else if (!LAST || !p.inverse) store_all(IntTag<0>());
     else if (p.scale_mode == 2) store_all(IntTag<2>());
     else store_all(IntTag<1>()); // cscale is 1 when the caller asked for no scaling
 }
 
 // Table builders: roots[i] = w_(2^log_roots)^i ; rscale[i] = 7^i / 2^logn.
-__global__ void k_build_roots(u64 *roots, u32 log_roots)
+// roots[i] = w_(2^log_roots)^(i << shift), i < count  (shift = 0: the table itself; shift = log_lo: the second-level table)
+__global__ void k_build_roots(u64 *roots, u32 log_roots, u64 count, u32 shift)
 {
-    const u64 n = 1ULL << log_roots;
-    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x)
-        roots[i] = gl::canon(pow_tab(c_w32, (u32)(i << (32 - log_roots))));
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (u64)gridDim.x * blockDim.x)
+        roots[i] = gl::canon(pow_tab(c_w32, (u32)((i << shift) << (32 - log_roots))));
 }
 __global__ void k_build_rscale(u64 *rscale, u32 logn)
 {

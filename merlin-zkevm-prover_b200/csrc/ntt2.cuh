@@ -128,7 +128,8 @@ k_pass2(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUte
         u64 twv = 0;
         if (newstrip) {
             spar ^= 1;
-            twv = p.roots[(u64)((u32)(low << tw_shift)) * tid];
+            const u32 ti = (u32)(low << tw_shift) * tid;
+            twv = p.roots_hi ? gl::mul(p.roots[ti & ((1u << p.log_lo) - 1)], p.roots_hi[ti >> p.log_lo]) : p.roots[ti];
         }
         tma::mbar_wait(&full[b], (u32)((q / NBUF) & 1));
 
@@ -212,7 +213,7 @@ k_pass2(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUte
                         if (colok) *lp = gl::canon(v);
                     } else {
                         const u64 row = (0 - (out_base + ((u64)(k0 + kc) << p.log_prev))) & nmask;
-                        v = gl::mul(v, LMODE == 1 ? p.cscale : p.rscale[row]);
+                        v = gl::mul(v, LMODE == 1 ? p.cscale : (p.rscale ? p.rscale[row] : gl::mul(pow_tab(c_p7, (u32)row), c_inv2[p.logn])));
                         if (colok) p.dst[row * p.dpitch + col] = gl::canon(v);
                     }
                 }

@@ -122,3 +122,48 @@ def test_group_proofs_batched(glb, oracle, fixtures):
     assert np.array_equal(glb.rows_gather_dev(ds.ptr, w, idxs), a[idxs.astype(np.int64)])
     with pytest.raises(glb.GLError):
         glb.group_proofs_dev(ds.ptr, dt.ptr, h, w, [h])
+
+
+def test_domain_2p28_two_level_roots(glb, oracle):
+    """Domains above 2^27 (the reference's NTT_Goldilocks accepts up to 2^32, ntt_goldilocks.hpp:94-97): four 7-bit passes with the
+    two-level twiddle lookup and the on-the-fly extend scale.  A 2^28-point transform of a 3-sparse column is checked on sampled
+    outputs against the definition Y[k] = sum_j X[j] w^(jk) (ntt_goldilocks.cpp:166-232), then INTT o NTT = id on the same column and
+    the extend form INTT(delta_j)[i] = 7^i w^(-ij) / n (ntt_goldilocks.cpp:124-136)."""
+    logn = 28
+    n = 1 << logn
+    L = oracle.L
+    w = L.glo_root_of_unity(logn)
+    pts = {5: 123456789, (1 << 27) + 77: P - 3, n - 1: 0x0123456789ABCDEF}
+    d = glb.DeviceBuffer(n)
+    zeros = np.zeros(1 << 24, dtype=np.uint64)
+    for off in range(0, n, 1 << 24):
+        d.upload(zeros, word_offset=off)
+    for j, v in pts.items():
+        d.upload(np.array([v], dtype=np.uint64), word_offset=j)
+    o = glb.DeviceBuffer(n)
+    glb.ntt_dev(o.ptr, d.ptr, n, 1)
+    rng = np.random.default_rng(51)
+    ks = [0, 1, n - 1, n // 2, 1 << 27] + [int(k) for k in rng.integers(0, n, size=40)]
+    for k in ks:
+        want = 0
+        for j, v in pts.items():
+            want = L.glo_add(want, L.glo_mul(v, L.glo_pow(w, (j * k) % n)))
+        assert int(o.download(1, k)[0]) == want, k
+    glb.ntt_dev(o.ptr, o.ptr, n, 1, inverse=True)
+    for j, v in pts.items():
+        assert int(o.download(1, j)[0]) == v % P
+    for k in ks[:12]:
+        if k not in pts:
+            assert int(o.download(1, k)[0]) == 0
+    # extend: INTT of v * delta_j scaled by 7^i / n
+    glb.ntt_dev(o.ptr, d.ptr, n, 1, inverse=True, extend=True)
+    ninv = L.glo_inv(n % P)
+    for i in ks[:20]:
+        want = 0
+        for j, v in pts.items():
+            want = L.glo_add(want, L.glo_mul(v, L.glo_pow(w, (n - (i * j) % n) % n)))
+        want = L.glo_mul(L.glo_mul(want, ninv), L.glo_pow(7, i))
+        assert int(o.download(1, i)[0]) == want, i
+    # back to an ordinary domain afterwards (the tables are rebuilt)
+    a = rng.integers(0, P, size=(1 << 12, 3), dtype=np.uint64)
+    assert np.array_equal(glb.ntt_host(a), oracle.ntt(a))
