@@ -189,7 +189,8 @@ int gl_last_timings4(float ms[4]);
  *      rank hashes its E/world rows (poseidon_goldilocks.cpp:277-281) and builds its subtree
  *      (:283-300); the world subtree roots are gathered and the top log2(world) levels hashed on every
  *      rank.  Result: the same root and node values as the single-GPU call.
- *      Rank r owns columns [gl_mgpu_col_start(C, world, r), gl_mgpu_col_start(C, world, r+1)). */
+ *      Rank r owns columns [gl_mgpu_col_start(C, world, r), gl_mgpu_col_start(C, world, r+1)): a contiguous split balanced in
+ *      units of 8 columns (the sponge rate), so that no 8-word chunk of a row straddles two ranks' panels. */
 int gl_mgpu_unique_id(uint8_t id[128]);                      /* rank 0; broadcast the 128 bytes to all ranks */
 int gl_mgpu_init(const uint8_t id[128], int rank, int world); /* after gl_init(device); world in {1,2,4,8} */
 int gl_mgpu_shutdown(void);

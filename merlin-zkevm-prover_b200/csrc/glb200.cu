@@ -427,9 +427,14 @@ int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpit
 }
 
 // Columns per scratch block: as many as the scratch limit and half of the free device memory allow (wide blocks amortise the
-// per-strip twiddle gather of k_pass2 and the launch tails), a multiple of 32, at least 32.
+// launch tails), a multiple of 32, at least 32.  The free-memory query is a driver call that takes milliseconds when several
+// processes share a node (it showed up as 20 ms of idle stream per commit at 8 GPUs), so the answer is remembered per
+// (ncols, bytes per column, limit) and reused as long as the arena it was sized for is still there.
 u32 pick_col_block(u64 ncols, size_t bytes_per_col)
 {
+    static u64 k_ncols = 0, k_cb = 0;
+    static size_t k_bpc = 0, k_limit = 0;
+    if (k_cb && k_ncols == ncols && k_bpc == bytes_per_col && k_limit == g.scratch_limit && g.arena_bytes >= bytes_per_col * k_cb) return (u32)k_cb;
     size_t budget = g.scratch_limit, free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
         free_b += g.arena_bytes; // the arena is ours to reuse
@@ -439,6 +444,7 @@ u32 pick_col_block(u64 ncols, size_t bytes_per_col)
     cb = (cb / 32) * 32;
     if (cb < 32) cb = 32;
     if (cb > ncols) cb = ncols;
+    k_ncols = ncols; k_bpc = bytes_per_col; k_limit = g.scratch_limit; k_cb = cb;
     return (u32)cb;
 }
 // scratch pitch of a block of cb columns: whole 16-column tiles (tensor maps need an even pitch; k_pass2 reads / writes whole tiles)
@@ -668,8 +674,17 @@ int nccl_load()
     return GL_OK;
 }
 
-// first column of rank r when ncols columns are split over `world` ranks (balanced, contiguous)
-u64 col_start(u64 ncols, int world, int r) { return ncols * (u64)r / (u64)world; }
+// First column of rank r when ncols columns are split over `world` ranks: contiguous, balanced in units of 8 columns (the rate of the
+// Poseidon sponge, poseidon_goldilocks.cpp:229-265), so that after the exchange no 8-word chunk of a row straddles two panels and
+// the leaf kernel reads every chunk with eight independent loads; the ncols % 8 columns left over go to the last rank.  With fewer
+// than 8 columns per rank the split is balanced in single columns.
+u64 col_start(u64 ncols, int world, int r)
+{
+    if (r >= world) return ncols;
+    const u64 chunks = ncols / 8;
+    if (chunks < (u64)world) return ncols * (u64)r / (u64)world;
+    return 8 * (chunks * (u64)r / (u64)world);
+}
 
 // word offset of level l (0 = leaves) in a tree over h leaves (merklehash_goldilocks.hpp:25-28 layout)
 u64 level_offset(u64 h, u32 l)

@@ -9,8 +9,15 @@ import numpy as np
 
 
 def col_start(ncols, world, rank):
-    """First column owned by `rank` (balanced contiguous split; rank r owns [col_start(r), col_start(r+1)))."""
-    return ncols * rank // world
+    """First column owned by `rank` (rank r owns [col_start(r), col_start(r+1))): contiguous, balanced in units of 8 columns (the sponge
+    rate) so that no 8-word chunk of a row straddles two panels; the ncols % 8 left-over columns go to the last rank; balanced in
+    single columns when there are fewer than 8 per rank.  Twin of col_start in csrc/glb200.cu."""
+    if rank >= world:
+        return ncols
+    chunks = ncols // 8
+    if chunks < world:
+        return ncols * rank // world
+    return 8 * (chunks * rank // world)
 
 
 def col_range(ncols, world, rank):
