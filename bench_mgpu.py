@@ -108,8 +108,12 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
     hbm_peak, peak_src = peaks()
     leaf_perm, tree_perm = permutations(loge, ncols)
     leaf_bytes = (e * ncols * 8 + e * 32) / world
-    chunks = 5 if (rows % 64 == 0 and rows // 64 >= 1024) else (4 if (rows % 4 == 0 and rows // 4 >= 256) else 1)  # mgpu_exchange_and_hash in csrc/glb200.cu
-    first_frac = 1 / 64 if chunks == 5 else 1 / chunks
+    # mgpu_exchange_and_hash in csrc/glb200.cu: chunks of 1, 3, 9, ... waves of the leaf kernel (148 SMs x 4 CTAs x 128 rows), the last takes the rest
+    wave, size, done, chunks = 148 * 4 * 128, 148 * 4 * 128, 0, 0
+    while chunks < 7 and rows > wave * 4 and rows - done > 4 * size:
+        done, size, chunks = done + size, size * 3, chunks + 1
+    chunks += 1
+    first_frac = wave / rows if chunks > 1 else 1.0
     config = dict(config)
     config["parallelism"] = "column-split LDE x%d -> NCCL all-to-all -> row-block leaf hash + subtrees -> gathered root" % world
     line = {"metric": "commit_ext_elements_per_s", "value": e * ncols / (dev_ms / 1e3), "unit": "ext-elem/s", "n_gpus": world, "steps": args.steps,

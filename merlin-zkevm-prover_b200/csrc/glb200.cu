@@ -1367,19 +1367,23 @@ int mgpu_exchange_and_hash(const u64 *lde_cols, u64 *row_panels, u64 *subtree, u
     for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
     for (int p = 0; p < G; p++) rp.base[p] = (const u64 *)row_panels + rows * rp.start[p];
     // Row chunks of GROWING size: only the first chunk's transfer is exposed (the hashing of chunk j hides the transfer of chunk
-    // j+1, and hashing a row takes ~9x as long as moving it), so the first chunk is 1/64 of the rows and each next one <= 4x larger.
-    u64 bounds[8];
-    u64 J = 1;
+    // j+1, and hashing a row takes ~9x as long as moving it).  Every row costs the same, so a leaf launch runs in whole WAVES of
+    // resident CTAs and a chunk that is not a multiple of a wave wastes the rest of its last wave (five uneven chunks cost 30
+    // waves for 27.7 waves of work at 8 GPUs: +6 % on the leaf phase).  Chunks are therefore 1, 3, 9, ... waves, the last one
+    // takes what is left.
+    u64 bounds[9];
+    u64 J = 0;
     bounds[0] = 0;
-    if (rows % 64 == 0 && rows / 64 >= 1024) {
-        static const u64 cum64[5] = {1, 4, 12, 32, 64}; // chunk sizes 1, 3, 8, 20, 32 sixty-fourths
-        J = 5;
-        for (u64 j = 0; j < J; j++) bounds[j + 1] = rows / 64 * cum64[j];
-    } else if (rows % 4 == 0 && rows / 4 >= 256) {
-        J = 4;
-        for (u64 j = 0; j < J; j++) bounds[j + 1] = rows / 4 * (j + 1);
-    } else {
-        bounds[1] = rows;
+    {
+        u64 wave = (u64)g.sms * GLB_LEAF_MINBLOCKS * poseidon::kThreads; // rows hashed by one wave of the leaf kernel
+        if (const char *v = getenv("GLB_MGPU_WAVE_ROWS")) wave = strtoull(v, nullptr, 10) ? strtoull(v, nullptr, 10) : wave; // tests: chunked path on small shapes
+        u64 size = wave, done = 0;
+        while (J < 7 && rows > wave * 4 && rows - done > 4 * size) {
+            done += size;
+            bounds[++J] = done;
+            size *= 3;
+        }
+        bounds[++J] = rows;
     }
     CU(cudaEventRecord(g.ev[5], g.stream));
     CU(cudaStreamWaitEvent(g.s_comm, g.ev[5], 0)); // the column block is complete

@@ -88,6 +88,7 @@ def main():
         dist.broadcast(idt, 0)
         glb.mgpu_init(idt.cpu().numpy().tobytes(), rank, world)
 
+    os.environ["GLB_MGPU_WAVE_ROWS"] = "16"   # small shapes: make the exchange run in several row chunks, as it does at full size
     for (n, e, ncols) in SHAPES:
         x, _ = o.xorshift(n * ncols)
         x = x.reshape(n, ncols)
@@ -152,6 +153,7 @@ def main():
             assert np.array_equal(hpan[:rows * ncols], pan), "host-pointer panels differ"
             assert np.array_equal(hsub, sub_dev), "host-pointer subtree differs"
         dist.barrier()
+    os.environ.pop("GLB_MGPU_WAVE_ROWS", None)
     if mode == "nccl" and os.environ.get("GLB_MGPU_FULL") == "1":
         full_size_check(glb, o, rank, world)
         dist.barrier()
