@@ -172,6 +172,14 @@ int gl_fri_layer_commit_dev(uint64_t *tree, uint64_t *aux, uint64_t *pol2, const
                             uint32_t next_bits, uint32_t tree_bits, uint64_t shift_inv, const uint64_t x[3],
                             uint64_t root[4]);
 
+/* Host-pointer forms of gl_q_commit_dev / gl_fri_layer_commit_dev: HOST buffers in and out (outputs may be NULL when not wanted),
+ * synchronous, copies included -- the literal replacements of starks.cpp:261-290 and of one step of friProve.cpp:36-126 for a caller
+ * that keeps its polynomials in host memory. */
+int gl_q_commit_host(uint64_t *cm4_host, uint64_t *tree_host, const uint64_t *q_2ns_host, uint64_t n, uint64_t n_ext, uint64_t qdim,
+                     uint64_t qdeg, uint64_t root[4]);
+int gl_fri_layer_commit_host(uint64_t *tree_host, uint64_t *aux_host, uint64_t *pol2_host, const uint64_t *pol_host, uint32_t pol_bits,
+                             uint32_t next_bits, uint32_t tree_bits, uint64_t shift_inv, const uint64_t x[3], uint64_t root[4]);
+
 /* Offline constant tree, the `bctree` tool (tools/starkpil/bctree/build_const_tree.cpp:333-407, GL branch): the
  * .consttree image [nPols, nExt, nExt x nPols extended constants, (2 nExt - 1) x 4 nodes] that
  * MerkleTreeGL(Goldilocks::Element *tree) re-opens (merkleTreeGL.hpp:24-32, starks.hpp:190).  Its interpolate()

@@ -76,6 +76,8 @@ SIGNATURES = {
     "gl_fri_fold_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, _u64, _u64p]),
     "gl_fri_transpose_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, C.c_uint32]),
     "gl_fri_layer_commit_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, _u64, _u64p, _u64p]),
+    "gl_q_commit_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64, _u64p]),
+    "gl_fri_layer_commit_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, _u64, _u64p, _u64p]),
     "gl_consttree_num_elements": (_u64, [_u64, _u64]),
     "gl_build_consttree_host": (C.c_int, [_u64p, _u64p, _u64, _u64, _u64]),
     "gl_last_timings4": (C.c_int, [C.POINTER(C.c_float)]),

@@ -84,6 +84,7 @@ struct Ctx {
     const void *res_host = nullptr;
     u64 res_rows = 0, res_cols = 0;
     void *res_lde = nullptr, *res_tree = nullptr;
+    int ntt_prefetch = 0;       // k_pass: L2 prefetch distance in units of the resident CTAs (0 off); env GLB_NTT_PREFETCH
     int ntt_variant = 0;        // 0: k_pass (direct loads, two CTAs per SM alternate load and butterfly phases -- the faster one),
                                 // 2 / 3: k_pass2 (ntt2.cuh: TMA / cp.async ring of 2 / 3 tile buffers); env GLB_NTT or gl_set_ntt_variant
     int sms = 148;
@@ -246,21 +247,33 @@ int ensure_rscale(u32 logn)
     return GL_OK;
 }
 
-template <int B2, bool LAST, int CW>
-int launch_pass_cw(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
+template <int B2, bool LAST, int CW, bool BIG>
+int launch_pass_inst(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
 {
     constexpr int R = 16 << B2;
     size_t smem = B2 > 0 ? (size_t)R * ntt::kTileCols * 8 : 0;
     static bool attr_done[16] = {false}; // per device: the attribute belongs to the device's copy of the function
     if (!attr_done[g.device & 15] && smem > 48 * 1024) {
-        CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST, CW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST, CW, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_done[g.device & 15] = true;
     }
     dim3 grid((unsigned)(ntiles / (ntt::kTileCols / CW)), coltiles), block(32, 1 << B2);
-    ntt::k_pass<B2, LAST, CW><<<grid, block, smem, g.stream>>>(p);
+    ntt::PassParams q = p;
+    q.pf_dist = (u32)(g.ntt_prefetch * g.sms * (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))); // resident CTAs per SM as in __launch_bounds__
+    ntt::k_pass<B2, LAST, CW, BIG><<<grid, block, smem, g.stream>>>(q);
     g.launches++;
     CU(cudaGetLastError());
     return GL_OK;
+}
+template <int B2, bool LAST, int CW>
+int launch_pass_cw(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
+{
+    // domains above 2^27: only the full-width tiles of 7- and 8-bit passes exist there (2^28 = 7+7+7+7 ... 2^32 = 8+8+8+8)
+    if (p.roots_hi || (p.scale_mode == 2 && !p.rscale)) {
+        if constexpr (B2 >= 3 && CW == ntt::kTileCols) return launch_pass_inst<B2, LAST, CW, true>(p, ntiles, coltiles);
+        else return fail(GL_ERR_ARG, "NTT above 2^27: unexpected pass shape");
+    }
+    return launch_pass_inst<B2, LAST, CW, false>(p, ntiles, coltiles);
 }
 
 // Full 32-column tiles in one launch; a ragged remainder of <= 16 (<= 8) columns in a second launch that packs two
@@ -887,6 +900,7 @@ int gl_init(int device)
     if (prop.major < 10) return fail(GL_ERR_CUDA, "device %s is sm_%d%d; this library is built for sm_100a only", prop.name, prop.major, prop.minor);
     g.sms = prop.multiProcessorCount;
     if (const char *v = getenv("GLB_NTT")) g.ntt_variant = atoi(v);
+    if (const char *v = getenv("GLB_NTT_PREFETCH")) g.ntt_prefetch = atoi(v);
     if (const char *v = getenv("GLB_SCRATCH_MIB")) g.scratch_limit = (size_t)atoll(v) << 20; // tuning runs (tools/): same as gl_set_scratch_limit
     CU(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g.s_h2d, cudaStreamNonBlocking));
@@ -1690,6 +1704,46 @@ int gl_fri_layer_commit_dev(uint64_t *tree, uint64_t *aux, uint64_t *pol2, const
     TRY(merkletree_dev((u64 *)tree, (const u64 *)aux, group * 3, ngroups, true));          // :120-123
     if (root) CU(cudaMemcpyAsync(root, tree + gl_tree_num_elements(ngroups) - 4, 32, cudaMemcpyDeviceToHost, g.stream));
     return collect_timings(false, true);
+}
+
+// Host-pointer forms of the two callers above (what a Starks / FRIProve that keeps its polynomials in host memory calls): upload,
+// the device-resident call, download of whatever the caller asked for (NULL = not wanted).
+int gl_q_commit_host(uint64_t *cm4_host, uint64_t *tree_host, const uint64_t *q_2ns_host, uint64_t n, uint64_t n_ext, uint64_t qdim,
+                     uint64_t qdeg, uint64_t root[4])
+{
+    API_ENTER();
+    if (n == 0 || n_ext == 0 || qdim == 0 || qdeg == 0) return fail(GL_ERR_ARG, "q_commit: empty input");
+    DevBuf q, cm4, tree;
+    const size_t qb = (size_t)n_ext * qdim * 8, cb = qb * qdeg, tb = gl_tree_num_elements(n_ext) * 8;
+    TRY(q.alloc(qb));
+    TRY(cm4.alloc(cb));
+    TRY(tree.alloc(tb));
+    CU(cudaMemcpyAsync(q.p, q_2ns_host, qb, cudaMemcpyHostToDevice, g.stream));
+    TRY(gl_q_commit_dev(cm4.w(), tree.w(), q.w(), n, n_ext, qdim, qdeg, root));
+    if (cm4_host) CU(cudaMemcpyAsync(cm4_host, cm4.p, cb, cudaMemcpyDeviceToHost, g.stream));
+    if (tree_host) CU(cudaMemcpyAsync(tree_host, tree.p, tb, cudaMemcpyDeviceToHost, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
+
+int gl_fri_layer_commit_host(uint64_t *tree_host, uint64_t *aux_host, uint64_t *pol2_host, const uint64_t *pol_host, uint32_t pol_bits,
+                             uint32_t next_bits, uint32_t tree_bits, uint64_t shift_inv, const uint64_t x[3], uint64_t root[4])
+{
+    API_ENTER();
+    if (next_bits > pol_bits || tree_bits > next_bits) return fail(GL_ERR_ARG, "fri_layer: bits %u -> %u, tree 2^%u", pol_bits, next_bits, tree_bits);
+    DevBuf pol, pol2, aux, tree;
+    const size_t pb = (size_t)24 << pol_bits, nb = (size_t)24 << next_bits, tb = gl_tree_num_elements(1ULL << tree_bits) * 8;
+    TRY(pol.alloc(pb));
+    TRY(pol2.alloc(nb));
+    TRY(aux.alloc(nb));
+    TRY(tree.alloc(tb));
+    CU(cudaMemcpyAsync(pol.p, pol_host, pb, cudaMemcpyHostToDevice, g.stream));
+    TRY(gl_fri_layer_commit_dev(tree.w(), aux.w(), pol2.w(), pol.w(), pol_bits, next_bits, tree_bits, shift_inv, x, root));
+    if (pol2_host) CU(cudaMemcpyAsync(pol2_host, pol2.p, nb, cudaMemcpyDeviceToHost, g.stream));
+    if (aux_host) CU(cudaMemcpyAsync(aux_host, aux.p, nb, cudaMemcpyDeviceToHost, g.stream));
+    if (tree_host) CU(cudaMemcpyAsync(tree_host, tree.p, tb, cudaMemcpyDeviceToHost, g.stream));
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
 }
 
 // ---- offline constant tree (tools/starkpil/bctree/build_const_tree.cpp:333-407) -------------------------

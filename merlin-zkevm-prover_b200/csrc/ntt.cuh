@@ -135,6 +135,8 @@ struct PassParams {
     // of w_(2^log_roots) and roots_hi[j] = w^(j * 2^log_lo); a twiddle is the product of one entry of each.  nullptr otherwise.
     const u64 *roots_hi;
     u32 log_lo;
+    u32 pf_dist;        // k_pass: prefetch into L2 the tile of the CTA `pf_dist` row-tiles ahead (= the CTAs resident at once: the next one
+                        // to get this SM slot), so that its loads hit L2 instead of HBM; 0 = off
 };
 
 template <int B2, bool CSEL = false> struct Step2 {
@@ -154,7 +156,9 @@ template <int B2, bool CSEL = false> struct Step2 {
 //   CW < 32 (ragged last column tile): the 32 lanes of a warp are 32/CW row-tiles x CW columns, so a block of
 //   11 columns keeps 22 of 32 lanes busy instead of 11; tile index and inter-pass twiddle then differ between the
 //   lane groups (per-lane instead of warp-uniform), everything that depends only on threadIdx.y stays uniform.
-template <int B2, bool LAST, int CW = kTileCols>
+// BIG: two-level twiddle lookup / on-the-fly extend scale of the domains above 2^27 -- a separate instantiation, so that the kernel of
+// the ordinary domains carries no second copy of its store loop (it cost 6 % of the c2 LDE as a run-time branch: instruction cache).
+template <int B2, bool LAST, int CW = kTileCols, bool BIG = false>
 __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k_pass(const PassParams p)
 {
     constexpr int R2 = 1 << B2;
@@ -184,6 +188,23 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
         for (int i1 = 0; i1 < 16; i1++) {
             x[i1] = (u32)i1 < iv ? *sp : 0;
             sp += sstep;
+        }
+        if (CW == kTileCols && p.pf_dist && colok) { // the same rows of the tile pf_dist row-tiles ahead (same column tile)
+            const u64 tau2 = tau + p.pf_dist;
+            if (tau2 < gridDim.x) {
+                const u64 row2 = ((((tau2 >> p.log_rest) * R) << p.log_rest) + (tau2 & ((1ULL << p.log_rest) - 1))) + ((u64)t << p.log_rest);
+                u32 iv2 = 0;
+                if (p.nvalid > row2) {
+                    const u64 q = ((p.nvalid - row2 - 1) >> rshift) + 1;
+                    iv2 = q < 16 ? (u32)q : 16u;
+                }
+                const u64 *pp = p.src + row2 * p.spitch + col;
+#pragma unroll
+                for (int i1 = 0; i1 < 16; i1++) {
+                    if ((u32)i1 < iv2) asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
+                    pp += sstep;
+                }
+            }
         }
     }
 
@@ -231,7 +252,7 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     const u64 lstep = p.dpitch << p.log_prev;
     u64 *lp = p.dst + (out_base + ((u64)k0 << p.log_prev)) * p.dpitch + col;
     auto store_all = [&](auto lmode_tag) {
-    constexpr int LMODE = decltype(lmode_tag)::value; // for !LAST: 3 = two-level twiddle lookup (domains above 2^27)
+    constexpr int LMODE = decltype(lmode_tag)::value;
     // walk the outputs in ascending kc so that the store pointer advances by compile-time multiples of dstep
     u32 kprev = 0;
 #pragma unroll
@@ -244,7 +265,7 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
         u64 v = x[i];
         if (!LAST) {
             const u32 ti = e1 * (k0 + kc);
-            if (LMODE == 3) v = gl::mul(gl::mul(v, p.roots[ti & ((1u << p.log_lo) - 1)]), p.roots_hi[ti >> p.log_lo]);
+            if (BIG) v = gl::mul(gl::mul(v, p.roots[ti & ((1u << p.log_lo) - 1)]), p.roots_hi[ti >> p.log_lo]);
             else v = gl::mul(v, p.roots[ti]);
             dp0 += dstep * (kc - kprev);
             kprev = kc;
@@ -255,13 +276,12 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
             if (colok) *lp = gl::canon(v);
         } else {
             const u64 row = (0 - (out_base + ((u64)(k0 + kc) << p.log_prev))) & nmask;
-            v = gl::mul(v, LMODE == 1 ? p.cscale : (p.rscale ? p.rscale[row] : gl::mul(pow_tab(c_p7, (u32)row), c_inv2[p.logn])));
+            v = gl::mul(v, LMODE == 1 ? p.cscale : (BIG ? gl::mul(pow_tab(c_p7, (u32)row), c_inv2[p.logn]) : p.rscale[row]));
             if (colok) p.dst[row * p.dpitch + col] = gl::canon(v);
         }
     }
     };
-    if (!LAST && p.roots_hi) store_all(IntTag<3>());
-    else if (!LAST || !p.inverse) store_all(IntTag<0>());
+    if (!LAST || !p.inverse) store_all(IntTag<0>());
     else if (p.scale_mode == 2) store_all(IntTag<2>());
     else store_all(IntTag<1>()); // cscale is 1 when the caller asked for no scaling
 }

@@ -323,6 +323,12 @@ def test_q_polynomial_commit(glb, oracle, fixtures):
         wt = oracle.merkletree(want)
         assert np.array_equal(dtree.download(), wt)
         assert np.array_equal(root, wt[-4:])
+        # host-pointer form (gl_q_commit_host): same matrix, tree and root
+        import ctypes as C
+        q = np.ascontiguousarray(q, dtype=np.uint64)
+        hcm4, htree, hroot = np.zeros((e, 3 * qdeg), dtype=np.uint64), np.zeros(wt.size, dtype=np.uint64), np.zeros(4, dtype=np.uint64)
+        rc = glb.lib().gl_q_commit_host(hcm4.ctypes.data, htree.ctypes.data, q.ctypes.data, n, e, 3, qdeg, hroot.ctypes.data_as(C.POINTER(C.c_uint64)))
+        assert rc == 0 and np.array_equal(hcm4, want) and np.array_equal(htree, wt) and np.array_equal(hroot, wt[-4:])
 
 
 @pytest.mark.gpu
@@ -349,6 +355,15 @@ def test_fri_layer_commit(glb, oracle, fixtures):
             wt = oracle.merkletree(aux.reshape(1 << tb, -1))
             assert np.array_equal(dtree.download(), wt), (pb, nb, tb)
             assert np.array_equal(root, wt[-4:])
+            # host-pointer form (gl_fri_layer_commit_host)
+            import ctypes as C
+            hp = np.ascontiguousarray(pol, dtype=np.uint64)
+            hx = np.ascontiguousarray(x, dtype=np.uint64)
+            hpol2, haux, htree, hroot = np.zeros_like(want), np.zeros_like(want), np.zeros(wt.size, dtype=np.uint64), np.zeros(4, dtype=np.uint64)
+            u64p = C.POINTER(C.c_uint64)
+            rc = glb.lib().gl_fri_layer_commit_host(htree.ctypes.data, haux.ctypes.data, hpol2.ctypes.data, hp.ctypes.data, pb, nb, tb, int(si),
+                                                    hx.ctypes.data_as(u64p), hroot.ctypes.data_as(u64p))
+            assert rc == 0 and np.array_equal(hpol2, want) and np.array_equal(haux, aux) and np.array_equal(htree, wt) and np.array_equal(hroot, wt[-4:])
 
 
 @pytest.mark.gpu
