@@ -282,7 +282,8 @@ template <int B2, bool LAST>
 int launch_pass_t(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
 {
     const u32 rag = p.ncols % ntt::kTileCols;
-    if (B2 >= 3 && rag != 0 && rag <= 16 && ntiles >= 4) {
+    const bool big = p.roots_hi || (p.scale_mode == 2 && !p.rscale); // domains above 2^27: full-width tiles only (launch_pass_cw)
+    if (B2 >= 3 && rag != 0 && rag <= 16 && ntiles >= 4 && !big) {
         const u32 full = p.ncols - rag;
         if (full) {
             ntt::PassParams q = p;
@@ -417,7 +418,7 @@ int run_ntt(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpit
     p.roots = g.roots;
     p.log_roots = g.log_roots;
     p.rscale = g.rscale;
-    p.roots_hi = g.log_roots > kLogRootsLo ? g.roots_hi : nullptr;
+    p.roots_hi = logn > kLogRootsLo ? g.roots_hi : nullptr; // a one-pass transform after a big one still finds the two-level table in g: it reads no roots
     p.log_lo = kLogRootsLo;
     p.cscale = scale_mode == 1 ? hpow((P + 1) / 2, logn) : 1; // 2^-logn (1: unscaled)
     const bool v2 = pass2_usable(logn, m, p.bits, tmp, tpitch, ncols);
