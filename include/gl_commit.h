@@ -89,6 +89,16 @@ int gl_ntt_dev(uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols
 /* NTT_Goldilocks::extendPol (ntt_goldilocks.cpp:326-352): out[k][c] = P_c(7 * w_E^k), k < n_ext,
  * where P_c interpolates in[.][c] over the size-n subgroup.  out holds n_ext*ncols words. */
 int gl_extend_pol_dev(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
+/* No counterpart in the reference.  gl_extend_pol_dev for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): same arguments, same result, but the
+ * twiddle / coset-scale tables and the column-block scratch live in one fixed file-scope device array (33 MiB, held by every GPU
+ * that loads the library until the process exits) instead of cudaMalloc'ed buffers.  The call makes no cudaMalloc / cudaFree and
+ * calls no allocating library routine (run gl_init once beforehand: it creates the library's stream).  LIMIT: n_ext <= 2^16 (any
+ * ncols; columns go through the array in blocks of (2^22 / (n + n_ext)) columns); larger sizes fail with GL_ERR_RANGE and a message
+ * naming the limit.  All calls share the array, which keeps the last call's contents (nothing in it has to start at zero: every word
+ * is written before it is read); calls are serialised on the library's stream -- work that overlaps them on the GPU through a
+ * second copy of the library's state would race on the array. */
+int gl_extend_pol_dev_noalloc(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
 /* PoseidonGoldilocks::merkletree_avx / MerkleTreeGL::merkelize (poseidon_goldilocks.cpp:266-301,
  * merkleTreeGL.cpp:37-44): tree holds (2*nrows-1)*4 words, leaf digests first, root last. */
 int gl_merkletree_dev(uint64_t *tree, const uint64_t *src, uint64_t ncols, uint64_t nrows);

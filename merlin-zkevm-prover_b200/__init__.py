@@ -49,6 +49,7 @@ SIGNATURES = {
     "gl_stream": (C.c_void_p, []),
     "gl_ntt_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, C.c_int, C.c_int]),
     "gl_extend_pol_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, _u64]),
+    "gl_extend_pol_dev_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, _u64]),
     "gl_merkletree_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64]),
     "gl_merkletree_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, _u64, _u64, _u64]),
     "gl_merkletree_batch_host": (C.c_int, [_u64p, _u64p, _u64, _u64, _u64]),
@@ -213,6 +214,11 @@ def ntt_dev(dst, src, size, ncols, inverse=False, extend=False):
 
 def extend_pol_dev(out, inp, n_ext, n, ncols):
     _check(lib().gl_extend_pol_dev(C.c_void_p(out), C.c_void_p(inp), n_ext, n, ncols))
+
+
+def extend_pol_dev_noalloc(out, inp, n_ext, n, ncols):
+    """gl_extend_pol_dev without any device allocation (static scratch, n_ext <= 2^16)."""
+    _check(lib().gl_extend_pol_dev_noalloc(C.c_void_p(out), C.c_void_p(inp), n_ext, n, ncols))
 
 
 def merkletree_dev(tree, src, ncols, nrows):

@@ -1766,3 +1766,125 @@ int gl_last_timings4(float ms[4])
 }
 
 } // extern "C"
+
+// ---- allocation-free extendPol (no counterpart in the reference) ---------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): the
+// twiddle table, the coset-scale table and the column-block scratch of extend_pol_dev live in ONE file-scope device array of fixed
+// size instead of cudaMalloc'ed buffers.  Every GPU that loads the library holds the array (33.0 MiB) until the process exits.
+// Layout (words): [0, 2^16) roots w_(2^16)^i | [2^16, 2^17) 7^i / n of the last n | [2^17, 2^17 + 2^22) INTT result + pass scratch.
+// All calls share the array and it keeps the previous call's contents.  Nothing in it has to start at zero: a call writes every
+// word before reading it (the INTT writes all n x w coefficients, the first forward pass reads only rows < n and writes all
+// n_ext x w words of the pass scratch), the roots are built once per device and the scale table is rebuilt when n changes.
+// Calls are serialised on the library stream; two calls overlapping on the GPU (another process-wide user of the symbol) would race.
+constexpr unsigned kNoAllocLogMax = 16;                                     // n_ext <= 2^16
+constexpr unsigned long long kNoAllocRootWords = 1ULL << kNoAllocLogMax;
+constexpr unsigned long long kNoAllocScaleWords = 1ULL << kNoAllocLogMax;
+constexpr unsigned long long kNoAllocWorkWords = 1ULL << 22;                // (n + n_ext) * (columns per block)
+static __device__ __align__(256) unsigned long long s_noalloc[kNoAllocRootWords + kNoAllocScaleWords + kNoAllocWorkWords];
+
+namespace {
+struct NoAllocDev {
+    u64 *base = nullptr;   // DEVICE address of s_noalloc on this device (the symbol's name is only a host-side stand-in)
+    bool roots_built = false;
+    u32 log_scale = ~0u;   // n of the scale table currently in the array
+} na_dev[16];
+
+// once per device, with that device current
+int noalloc_setup(NoAllocDev **out)
+{
+    if (g.device < 0 || g.device >= 16) return fail(GL_ERR_ARG, "no-alloc extendPol: device %d out of range", g.device);
+    NoAllocDev &d = na_dev[g.device];
+    if (!d.base) {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, s_noalloc);
+        if (e != cudaSuccess || !ptr) return fail(GL_ERR_CUDA, "cudaGetSymbolAddress(s_noalloc): %s", cudaGetErrorString(e));
+        d.base = (u64 *)ptr;
+        d.roots_built = false;
+        d.log_scale = ~0u;
+    }
+    if (!d.roots_built) {
+        ntt::k_build_roots<<<148, 256, 0, g.stream>>>(d.base, kNoAllocLogMax, kNoAllocRootWords, 0);
+        g.launches++;
+        CU(cudaGetLastError());
+        d.roots_built = true;
+    }
+    *out = &d;
+    return GL_OK;
+}
+
+// run_ntt with caller-supplied tables, always through ntt::k_pass (no tensor maps)
+int run_ntt_tables(u64 *dst, u64 dpitch, const u64 *src, u64 spitch, u64 *tmp, u64 tpitch, u32 logn, u32 ncols, bool inverse,
+                   int scale_mode, u64 nvalid, const u64 *roots, u32 log_roots, const u64 *rscale)
+{
+    ntt::PassParams p;
+    memset(&p, 0, sizeof p);
+    p.ncols = ncols;
+    p.logn = logn;
+    p.inverse = inverse ? 1 : 0;
+    if (logn <= 3) {
+        p.src = src; p.dst = dst; p.spitch = spitch; p.dpitch = dpitch;
+        p.scale_mode = scale_mode; p.nvalid = nvalid; p.npass = 1;
+        ntt::k_tiny<<<(ncols + 127) / 128, 128, 0, g.stream>>>(p);
+        g.launches++;
+        CU(cudaGetLastError());
+        return GL_OK;
+    }
+    const u32 m = (logn + 7) / 8;
+    p.npass = m;
+    for (u32 i = 0; i < m; i++) p.bits[i] = logn / m + (i < logn % m ? 1 : 0);
+    p.roots = roots;
+    p.log_roots = log_roots;
+    p.rscale = rscale;
+    p.roots_hi = nullptr;
+    p.log_lo = kLogRootsLo;
+    p.cscale = scale_mode == 1 ? hpow((P + 1) / 2, logn) : 1;
+    u32 prev = 0;
+    for (u32 i = 0; i < m; i++) {
+        const bool first = i == 0, last = i + 1 == m;
+        p.pass = i;
+        p.log_prev = prev;
+        p.log_rest = logn - prev - p.bits[i];
+        p.src = first ? src : tmp;
+        p.spitch = first ? spitch : tpitch;
+        p.dst = last ? dst : tmp;
+        p.dpitch = last ? dpitch : tpitch;
+        p.nvalid = first ? nvalid : (1ULL << logn);
+        p.scale_mode = last ? scale_mode : 0;
+        TRY(launch_pass(p));
+        prev += p.bits[i];
+    }
+    return GL_OK;
+}
+} // namespace
+
+extern "C" int gl_extend_pol_dev_noalloc(uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols)
+{
+    API_ENTER();
+    if (n == 0 || ncols == 0) return GL_OK;
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "extendPol: bad sizes %llu -> %llu", (u64)n, (u64)n_ext);
+    if (n_ext > (1ULL << kNoAllocLogMax))
+        return fail(GL_ERR_RANGE, "gl_extend_pol_dev_noalloc: n_ext = %llu exceeds the static scratch (at most 2^%u extended rows); use gl_extend_pol_dev",
+                    (u64)n_ext, kNoAllocLogMax);
+    if (ncols > 0xFFFFFFFFULL) return fail(GL_ERR_ARG, "extendPol: %llu columns", (u64)ncols);
+    NoAllocDev *d = nullptr;
+    TRY(noalloc_setup(&d));
+    const u32 logn = ilog2(n), loge = ilog2(n_ext);
+    u64 *roots = d->base, *rscale = d->base + kNoAllocRootWords, *work = rscale + kNoAllocScaleWords;
+    if (d->log_scale != logn) { // stream order keeps the rebuild behind the previous call's readers
+        ntt::k_build_rscale<<<148, 256, 0, g.stream>>>(rscale, logn);
+        g.launches++;
+        CU(cudaGetLastError());
+        d->log_scale = logn;
+    }
+    u64 cb = kNoAllocWorkWords / (n + n_ext); // >= 32 at the largest size
+    if (cb > 32) cb = (cb / 32) * 32;
+    if (cb > ncols) cb = ncols;
+    u64 *coef = work, *tmp = work + n * cb;
+    for (u64 c0 = 0; c0 < ncols; c0 += cb) {
+        const u32 w = (u32)((ncols - c0 < cb) ? ncols - c0 : cb);
+        TRY(run_ntt_tables(coef, cb, (const u64 *)in + c0, ncols, tmp, cb, logn, w, true, 2, n, roots, kNoAllocLogMax, rscale));
+        TRY(run_ntt_tables((u64 *)out + c0, ncols, coef, cb, tmp, cb, loge, w, false, 0, n, roots, kNoAllocLogMax, rscale));
+    }
+    CU(cudaStreamSynchronize(g.stream));
+    return GL_OK;
+}
