@@ -44,7 +44,10 @@ int gl_init(int device);
 void gl_shutdown(void);
 const char *gl_last_error(void);
 int gl_device_count(int *count);
-/* Upper bound (bytes) for the library's internal scratch arena; 0 = default (32 GiB, and never more than half of the free device memory). */
+/* Upper bound (bytes) for the library's internal scratch arena; 0 = default (32 GiB, and never more than half of the free device memory).
+ * The call also hands back to the driver the device buffers that the *_host commit calls keep between calls (the extended matrix,
+ * the tree and the upload staging: allocating and freeing 80 GB costs 50-120 ms per call); the library releases them by itself
+ * whenever one of its own device allocations (gl_dev_alloc included) would otherwise fail. */
 int gl_set_scratch_limit(size_t bytes);
 /* Resident stage (off by default).  When on, gl_extend_pol_host -- NTT_Goldilocks::extendPol of the shims -- also hashes the
  * leaves and builds the tree while the extended matrix is being downloaded (the download hides it) and keeps the device copies

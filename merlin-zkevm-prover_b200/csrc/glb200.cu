@@ -84,6 +84,7 @@ struct Ctx {
     const void *res_host = nullptr;
     u64 res_rows = 0, res_cols = 0;
     void *res_lde = nullptr, *res_tree = nullptr;
+    size_t res_lde_bytes = 0, res_tree_bytes = 0;
     int ntt_prefetch = 0;       // k_pass: L2 prefetch distance in units of the resident CTAs (0 off); env GLB_NTT_PREFETCH
     int ntt_variant = 0;        // 0: k_pass (direct loads, two CTAs per SM alternate load and butterfly phases -- the faster one),
                                 // 2 / 3: k_pass2 (ntt2.cuh: TMA / cp.async ring of 2 / 3 tile buffers); env GLB_NTT or gl_set_ntt_variant
@@ -92,8 +93,34 @@ struct Ctx {
                                 // INTT on nX x 3 matrices from an OpenMP loop, friProve.cpp:44-107)
     u64 *qbuf = nullptr;        // grow-only staging of the batched query calls: [indices | gathered words] (device)
     size_t qbuf_words = 0;
+    // Device buffers of the host-pointer commit (extended matrix, tree, upload staging) kept between calls: cudaMalloc + cudaFree of
+    // the 80 GB matrix cost 50-120 ms of every c2 call (profiles/r2_29_alloc_cost.txt).  One buffer per slot, reused when large
+    // enough; given back to the driver by gl_shutdown, gl_set_resident(0), gl_set_scratch_limit and whenever a device allocation
+    // of the library fails (it then retries once).
+    struct PoolSlot { void *p = nullptr; size_t bytes = 0; } pool[3];
     std::mutex mu;
 } g;
+
+void pool_trim()
+{
+    for (auto &sl : g.pool) {
+        if (sl.p) cudaFree(sl.p);
+        sl.p = nullptr;
+        sl.bytes = 0;
+    }
+}
+
+// cudaMalloc that gives the cached buffers back to the driver and retries once when the device is full
+cudaError_t dev_malloc(void **p, size_t bytes)
+{
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e == cudaErrorMemoryAllocation && (g.pool[0].p || g.pool[1].p || g.pool[2].p)) {
+        cudaGetLastError(); // clear the sticky-free allocation error
+        pool_trim();
+        e = cudaMalloc(p, bytes);
+    }
+    return e;
+}
 
 // ---- host-side field helpers (table generation only) -------------------------------------------
 const u64 P = 0xFFFFFFFF00000001ULL;
@@ -171,7 +198,7 @@ int arena_reserve(size_t bytes)
         g.arena = nullptr;
         g.arena_bytes = 0;
     }
-    CU(cudaMalloc(&g.arena, bytes));
+    CU(dev_malloc(&g.arena, bytes));
     g.arena_bytes = bytes;
     return GL_OK;
 }
@@ -209,11 +236,11 @@ int ensure_roots(u32 logn)
         g.roots_hi = nullptr;
     }
     const u64 count = 1ULL << (big ? kLogRootsLo : L);
-    CU(cudaMalloc(&g.roots, count * 8));
+    CU(dev_malloc((void **)&g.roots, count * 8));
     ntt::k_build_roots<<<148 * 4, 256, 0, g.stream>>>(g.roots, L, count, 0);
     g.launches++;
     if (big) {
-        CU(cudaMalloc(&g.roots_hi, (size_t)8 << (L - kLogRootsLo)));
+        CU(dev_malloc((void **)&g.roots_hi, (size_t)8 << (L - kLogRootsLo)));
         ntt::k_build_roots<<<1, 32, 0, g.stream>>>(g.roots_hi, L, 1ULL << (L - kLogRootsLo), kLogRootsLo);
         g.launches++;
     }
@@ -239,7 +266,7 @@ int ensure_rscale(u32 logn)
         CU(cudaFree(g.rscale));
         g.rscale = nullptr;
     }
-    CU(cudaMalloc(&g.rscale, (size_t)8 << logn));
+    CU(dev_malloc((void **)&g.rscale, (size_t)8 << logn));
     ntt::k_build_rscale<<<148 * 4, 256, 0, g.stream>>>(g.rscale, logn);
     g.launches++;
     CU(cudaGetLastError());
@@ -452,6 +479,7 @@ u32 pick_col_block(u64 ncols, size_t bytes_per_col)
     size_t budget = g.scratch_limit, free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
         free_b += g.arena_bytes; // the arena is ours to reuse
+        for (const auto &sl : g.pool) free_b += sl.bytes; // and so are the cached host-path buffers (dev_malloc gives them back on demand)
         if (free_b / 2 < budget) budget = free_b / 2;
     }
     u64 cb = budget / bytes_per_col;
@@ -732,26 +760,93 @@ __global__ void k_fill_synthetic_cols(u64 *dst, u64 nrows, u64 col0, u64 w, u64 
     }
 }
 
-void resident_drop()
-{
-    if (g.res_lde) cudaFree(g.res_lde);
-    if (g.res_tree) cudaFree(g.res_tree);
-    g.res_lde = g.res_tree = nullptr;
-    g.res_host = nullptr;
-    g.res_rows = g.res_cols = 0;
-}
-
 struct DevBuf {
     void *p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
     void *release() { void *q = p; p = nullptr; return q; }
     int alloc(size_t bytes)
     {
-        CU(cudaMalloc(&p, bytes ? bytes : 8));
+        CU(dev_malloc(&p, bytes ? bytes : 8));
         return GL_OK;
     }
     uint64_t *w() { return (uint64_t *)p; }
 };
+
+// A buffer taken from pool slot `slot` (or freshly allocated) and put back there when the call ends.
+struct PoolBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    int slot;
+    explicit PoolBuf(int s) : slot(s) {}
+    ~PoolBuf() { put_back(p, bytes); }
+    void put_back(void *q, size_t b)
+    {
+        if (!q) return;
+        Ctx::PoolSlot &sl = g.pool[slot];
+        if (sl.p && sl.bytes >= b) { cudaFree(q); return; } // the slot already holds a buffer at least as large
+        if (sl.p) cudaFree(sl.p);
+        sl.p = q;
+        sl.bytes = b;
+    }
+    int alloc(size_t want)
+    {
+        if (!want) want = 8;
+        Ctx::PoolSlot &sl = g.pool[slot];
+        if (sl.p && sl.bytes >= want) {
+            p = sl.p; bytes = sl.bytes;
+            sl.p = nullptr; sl.bytes = 0;
+            return GL_OK;
+        }
+        if (sl.p) { cudaFree(sl.p); sl.p = nullptr; sl.bytes = 0; }
+        CU(dev_malloc(&p, want));
+        bytes = want;
+        return GL_OK;
+    }
+    void *release(size_t *b) { void *q = p; *b = bytes; p = nullptr; bytes = 0; return q; }
+};
+
+// Column blocks of the pipelined host-pointer calls: a narrow first block (32 columns) so that the download -- the bottleneck: 81.6 GB
+// on c2 -- starts after a short upload, a second block that completes the first `cb` columns, then blocks of `cb` columns.  Wide
+// blocks matter: a column-stripe copy moves w * 8 bytes per row and the copy engine sustains 55 GB/s at 128 columns but only 28 GB/s
+// at 32 (16 at 16) while the upload runs (profiles/r2_31_pcie_split_streams.txt; splitting a stripe over several streams does not
+// help, the copies of one direction share one engine).  A schedule that starts at 16 columns and grows by 1.75x per block was
+// measured 8 % SLOWER end to end (profiles/r2_30_e2e_block_schedule_ab.txt); GLB_HOST_BLOCKS=1 selects it for tuning runs.
+std::vector<u64> block_starts(u64 ncols, u64 cb)
+{
+    std::vector<u64> starts;
+    static const int sched = getenv("GLB_HOST_BLOCKS") ? atoi(getenv("GLB_HOST_BLOCKS")) : 0;
+    if (sched == 0) {
+        const bool graded = cb > 32 && ncols > 2 * cb;
+        for (u64 c0 = 0; c0 < ncols;) {
+            starts.push_back(c0);
+            c0 += (graded && c0 == 0) ? 32 : ((graded && c0 == 32) ? cb - 32 : cb);
+        }
+        starts.push_back(ncols);
+        return starts;
+    }
+    const bool graded = cb > 16 && ncols >= 64;
+    u64 w = graded ? (sched >= 8 ? (u64)sched : 16) : cb;
+    for (u64 c0 = 0; c0 < ncols;) {
+        starts.push_back(c0);
+        c0 += w;
+        if (graded && w < cb) {
+            w = ((w * 7 / 4) / 8) * 8;
+            if (w > cb) w = cb;
+        }
+    }
+    starts.push_back(ncols);
+    return starts;
+}
+
+void resident_drop()
+{
+    if (g.res_lde) { PoolBuf b(0); b.put_back(g.res_lde, g.res_lde_bytes); }   // back to the pool: the next host-pointer commit reuses them
+    if (g.res_tree) { PoolBuf b(1); b.put_back(g.res_tree, g.res_tree_bytes); }
+    g.res_lde = g.res_tree = nullptr;
+    g.res_lde_bytes = g.res_tree_bytes = 0;
+    g.res_host = nullptr;
+    g.res_rows = g.res_cols = 0;
+}
 
 // Host-pointer stage commit / extendPol, pipelined over column blocks: while block k is transformed on the
 // compute stream, block k+1 is uploaded (strided 2-D copy out of the row-major host matrix) and the finished
@@ -766,7 +861,7 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
     if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GL_ERR_ARG, "extendPol: bad sizes %llu -> %llu", n, n_ext);
     if (n_ext > (1ULL << 32)) return fail(GL_ERR_RANGE, "Domain size too big for the curve");
     const u32 logn = ilog2(n), loge = ilog2(n_ext);
-    DevBuf l, t, stage;
+    PoolBuf l(0), t(1), stage(2);
     TRY(l.alloc((size_t)n_ext * ncols * 8));
     if (do_tree) TRY(t.alloc(gl_tree_num_elements(n_ext) * 8));
     u64 *lde = (u64 *)l.p;
@@ -776,7 +871,7 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         if (cb > 128) cb = 128;
         size_t free_b = 0, total_b = 0;
         CU(cudaMemGetInfo(&free_b, &total_b));
-        free_b += g.arena_bytes;
+        free_b += g.arena_bytes + g.pool[2].bytes; // ours to reuse: the arena and the cached staging block
         const size_t per_col = (size_t)(3 * n + n_ext) * 8; // coef + pass scratch + two staging buffers
         while (cb > 32 && per_col * cb + ((size_t)1 << 30) > free_b) cb -= 32;
         if (cb > ncols) cb = ncols;
@@ -784,19 +879,23 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         TRY(arena_reserve((size_t)(n + n_ext) * cp * 8));
         TRY(stage.alloc((size_t)2 * n * cb * 8));
         u64 *coef = (u64 *)g.arena, *tmp = coef + (size_t)n * cp;
-        // block boundaries: a narrow first block so that compute starts after a short upload, then full-width blocks
-        std::vector<u64> starts;
-        const bool graded = cb > 32 && ncols > 2 * cb;
-        for (u64 c0 = 0; c0 < ncols;) {
-            starts.push_back(c0);
-            c0 += (graded && c0 == 0) ? 32 : ((graded && c0 == 32) ? cb - 32 : cb);
-        }
-        starts.push_back(ncols);
+        const std::vector<u64> starts = block_starts(ncols, cb);
         const u64 nb = starts.size() - 1;
-        std::vector<cudaEvent_t> ev_in(nb), ev_done(nb);
+        // GLB_HOST_TRACE=1 (tuning runs): timed events, the per-block timeline goes to stderr after the call
+        static const bool trace = getenv("GLB_HOST_TRACE") && atoi(getenv("GLB_HOST_TRACE")) != 0;
+        const unsigned evflags = trace ? cudaEventDefault : cudaEventDisableTiming;
+        std::vector<cudaEvent_t> ev_in(nb), ev_done(nb), ev_hash, ev_dn;
+        cudaEvent_t ev_t0 = nullptr;
         for (u64 k = 0; k < nb; k++) {
-            CU(cudaEventCreateWithFlags(&ev_in[k], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&ev_done[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&ev_in[k], evflags));
+            CU(cudaEventCreateWithFlags(&ev_done[k], evflags));
+        }
+        if (trace) {
+            ev_hash.resize(nb);
+            ev_dn.resize(nb);
+            for (u64 k = 0; k < nb; k++) { CU(cudaEventCreate(&ev_hash[k])); CU(cudaEventCreate(&ev_dn[k])); }
+            CU(cudaEventCreate(&ev_t0));
+            CU(cudaEventRecord(ev_t0, g.s_h2d));
         }
         int rc = GL_OK;
         for (u64 k = 0; k < nb && rc == GL_OK; k++) {
@@ -814,10 +913,27 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
                 poseidon::k_linear_hash_partial<<<poseidon::grid_for(n_ext), poseidon::kThreads, 0, g.stream>>>((u64 *)t.p, lde, n_ext, ncols, (u32)c0, w);
                 g.launches++;
             }
+            if (trace) CUP(cudaEventRecord(ev_hash[k], g.stream));
             if (lde_out) {
                 CUP(cudaStreamWaitEvent(g.s_d2h, ev_done[k], 0));
                 CUP(cudaMemcpy2DAsync(lde_out + c0, ncols * 8, lde + c0, ncols * 8, (size_t)w * 8, n_ext, cudaMemcpyDeviceToHost, g.s_d2h));
             }
+            if (trace) CUP(cudaEventRecord(ev_dn[k], g.s_d2h));
+        }
+        if (trace && rc == GL_OK) {
+            cudaDeviceSynchronize();
+            fprintf(stderr, "[glb200 host trace] %llu blocks of %llu x %llu -> %llu (ms since the first upload started)\n", (u64)nb, (u64)n, (u64)ncols, (u64)n_ext);
+            for (u64 k = 0; k < nb; k++) {
+                float a = 0, b = 0, c = 0, d = 0;
+                cudaEventElapsedTime(&a, ev_t0, ev_in[k]);
+                cudaEventElapsedTime(&b, ev_t0, ev_done[k]);
+                cudaEventElapsedTime(&c, ev_t0, ev_hash[k]);
+                cudaEventElapsedTime(&d, ev_t0, ev_dn[k]);
+                fprintf(stderr, "  block %2llu cols %4llu..%4llu  uploaded %8.1f  extended %8.1f  hashed %8.1f  downloaded %8.1f\n", (u64)k, (u64)starts[k],
+                        (u64)starts[k + 1], a, b, c, d);
+            }
+            for (u64 k = 0; k < nb; k++) { cudaEventDestroy(ev_hash[k]); cudaEventDestroy(ev_dn[k]); }
+            cudaEventDestroy(ev_t0);
         }
         cudaError_t e = cudaGetLastError();
         if (rc == GL_OK && e != cudaSuccess) rc = fail(GL_ERR_CUDA, "pipelined commit: %s", cudaGetErrorString(e));
@@ -846,8 +962,8 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         g.res_host = lde_out;
         g.res_rows = n_ext;
         g.res_cols = ncols;
-        g.res_lde = l.release();
-        g.res_tree = t.release();
+        g.res_lde = l.release(&g.res_lde_bytes);
+        g.res_tree = t.release(&g.res_tree_bytes);
     }
     return GL_OK;
 }
@@ -929,6 +1045,7 @@ void gl_shutdown(void)
     if (g.roots_hi) cudaFree(g.roots_hi);
     g.roots_hi = nullptr;
     resident_drop();
+    pool_trim();
     if (g.small_dev) cudaFree(g.small_dev);
     g.small_dev = nullptr;
     if (g.qbuf) cudaFree(g.qbuf);
@@ -951,7 +1068,10 @@ int gl_set_resident(int on)
 {
     std::lock_guard<std::recursive_mutex> api_lock_(g_api_mu);
     g.resident_on = on != 0;
-    if (!g.resident_on && g.ready) resident_drop();
+    if (!g.resident_on && g.ready) {
+        resident_drop();
+        pool_trim(); // turning the mode off hands the memory back
+    }
     return GL_OK;
 }
 
@@ -973,7 +1093,9 @@ int gl_set_ntt_variant(int v)
 
 int gl_set_scratch_limit(size_t bytes)
 {
+    std::lock_guard<std::recursive_mutex> api_lock_(g_api_mu);
     g.scratch_limit = bytes ? bytes : ((size_t)32 << 30);
+    if (g.ready) pool_trim(); // also gives the buffers cached by the host-pointer commit back to the driver
     return GL_OK;
 }
 
@@ -987,7 +1109,7 @@ uint64_t gl_kernel_launches(int reset)
 int gl_dev_alloc(void **dptr, size_t bytes)
 {
     API_ENTER();
-    CU(cudaMalloc(dptr, bytes ? bytes : 8));
+    CU(dev_malloc(dptr, bytes ? bytes : 8));
     return GL_OK;
 }
 int gl_dev_free(void *dptr)
@@ -1113,7 +1235,7 @@ static int qbuf_reserve(size_t words)
         g.qbuf_words = 0;
     }
     size_t cap = words < 4096 ? 4096 : words + words / 2;
-    CU(cudaMalloc(&g.qbuf, cap * 8));
+    CU(dev_malloc((void **)&g.qbuf, cap * 8));
     g.qbuf_words = cap;
     return GL_OK;
 }

@@ -235,6 +235,25 @@ def test_config1_commit_every_word(glb, oracle, kats):
     assert np.array_equal(tree[-4:], root)
 
 
+def test_commit_host_blocks_and_buffer_reuse(glb, oracle):
+    """The host-pointer commit walks the columns in blocks (32, 96, 128, 128 ... columns: upload of block k+1, LDE + leaf sponge of
+    block k and download of block k-1 overlap) and keeps its device buffers between calls.  A ragged width that takes five blocks,
+    twice in a row (the second call reuses the cached buffers), then a smaller and a larger shape through the same buffers, then
+    again after the cache was handed back (gl_set_scratch_limit)."""
+    rng = np.random.default_rng(81)
+    for (n, e, c) in [(1 << 9, 1 << 11, 395), (1 << 9, 1 << 11, 395), (1 << 8, 1 << 9, 70), (1 << 10, 1 << 12, 403)]:
+        a = rng.integers(0, P, size=(n, c), dtype=np.uint64)
+        lde, tree, root = glb.commit_host(a, e)
+        lde_o = oracle.extend_pol(a, e)
+        assert np.array_equal(lde, lde_o), (n, e, c)
+        assert np.array_equal(tree, oracle.merkletree(lde_o)), (n, e, c)
+        assert np.array_equal(root, tree[-4:])
+        assert np.array_equal(glb.extend_pol_host(a, e), lde_o), (n, e, c)
+    glb.lib().gl_set_scratch_limit(0)
+    lde, tree, root = glb.commit_host(a, e)
+    assert np.array_equal(lde, lde_o) and np.array_equal(tree, oracle.merkletree(lde_o))
+
+
 def test_recursive_shape_high_blowup(glb, oracle):
     """BASELINE.json configs[3] shape at reduced size: blowup 2^4."""
     rng = np.random.default_rng(8)
