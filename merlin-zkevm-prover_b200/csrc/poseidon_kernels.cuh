@@ -117,7 +117,7 @@ __device__ __forceinline__ void linear_hash_row(u64 *d, const RowPanels &rp, con
 
 // One thread per row: leaf digests of MerkleTreeGL::merkelize (poseidon_goldilocks.cpp:277-281).
 template <bool PANELS>
-__global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_linear_hash_rows(u64 *__restrict__ digests, const RowPanels rp, u64 nrows, u32 ncols)
+__global__ void __launch_bounds__(kThreads, GLB_LEAF_MINBLOCKS) k_linear_hash_rows(u64 *__restrict__ digests, const __grid_constant__ RowPanels rp, u64 nrows, u32 ncols)
 {
     u64 row = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nrows) return;
