@@ -1,7 +1,7 @@
 """bench_mgpu.py -- the N>1 leg of bench.py (one process per GPU, launched by torchrun).
 
 The stage commit of the workload is sharded as SURVEY 8e / DESIGN.md "Multi-GPU": columns split over ranks
-for the LDE, NCCL all-to-all (grouped ncclSend/ncclRecv over NVLink) to row blocks, per-rank leaf hashing +
+for the LDE, all-to-all over NVLink (peer copies through the copy engines; grouped ncclSend/ncclRecv as the fallback) to row blocks, per-rank leaf hashing +
 subtree, gathered roots -> top levels.  Total work is fixed as N grows ("strong" scaling of BASELINE config 3);
 value = E*C / (max over ranks of the device time of one step).
 """
@@ -100,6 +100,7 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
                 if hp.value:
                     L.gl_host_free(hp)
 
+    exchange_mode = glb.lib().gl_mgpu_exchange_mode()
     glb.mgpu_shutdown()
     if rank != 0:
         return 0
@@ -126,6 +127,8 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
             "ms_per_rank": {"columns": ["step", "lde", "exchange", "leaf", "tree"], "rows": per_rank},
             "phases": {"lde": {"ms": lde_ms},
                        "exchange": {"ms": ex_ms, "bytes_sent_per_rank": (world - 1) * rows * w * 8, "row_chunks": chunks,
+                                    "transport": ("peer cudaMemcpyAsync over NVLink through the copy engines into CUDA-IPC mappings of the peers' panels, one-word ncclAllGather as the barrier"
+                                                  if exchange_mode == 1 else "grouped ncclSend/ncclRecv"),
                                     "note": "exposed part only: the rows are exchanged in %d chunks of growing size (first %.4f of the rows) on a second stream; chunk j+1 moves while chunk j is hashed" % (chunks, first_frac),
                                     "GBps_per_rank_first_chunk": (world - 1) * rows * w * 8 * first_frac / max(ex_ms, 1e-9) / 1e6},
                        "leaf": {"ms": leaf_ms, "permutations_per_rank": leaf_perm // world}, "tree": {"ms": tree_ms}},

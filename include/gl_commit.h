@@ -216,6 +216,10 @@ int gl_mgpu_unique_id(uint8_t id[128]);                      /* rank 0; broadcas
 int gl_mgpu_init(const uint8_t id[128], int rank, int world); /* after gl_init(device); world in {1,2,4,8} */
 int gl_mgpu_shutdown(void);
 uint64_t gl_mgpu_col_start(uint64_t ncols, int world, int rank);
+/* How the last gl_commit_mgpu[_host] moved the column blocks into row panels: 1 = copy engines (every rank maps the peers' row_panels
+ * buffers through CUDA IPC -- they must come from cudaMalloc / gl_dev_alloc -- and pushes its rows into them with peer copies over
+ * NVLink, no SM involved; the default), 0 = grouped ncclSend/ncclRecv (GLB_MGPU_EXCHANGE=nccl, or when a buffer could not be mapped). */
+int gl_mgpu_exchange_mode(void);
 /* in_cols: n x w (this rank's w columns, row-major, pitch w); lde_cols: n_ext x w (out: this rank's
  * columns of the LDE); row_panels: (n_ext/world) * ncols_total words (out: this rank's rows, stored as
  * `world` panels -- panel p at word offset (n_ext/world)*col_start(p), row-major with pitch w_p);

@@ -86,6 +86,7 @@ SIGNATURES = {
     "gl_mgpu_init": (C.c_int, [C.POINTER(C.c_uint8), C.c_int, C.c_int]),
     "gl_mgpu_shutdown": (C.c_int, []),
     "gl_mgpu_col_start": (_u64, [_u64, C.c_int, C.c_int]),
+    "gl_mgpu_exchange_mode": (C.c_int, []),
     "gl_commit_mgpu": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64p]),
     "gl_commit_mgpu_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, _u64, _u64, _u64, _u64p]),
     "gl_mgpu_gather_tree": (C.c_int, [C.c_void_p, C.c_void_p, _u64]),

@@ -684,7 +684,19 @@ struct Nccl {
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
     u64 *top = nullptr; // (2*world-1)*4 words: gathered subtree roots + the levels above them
+    // Copy-engine exchange (default; GLB_MGPU_EXCHANGE=nccl selects grouped ncclSend/ncclRecv): every rank maps the peers' row-panel
+    // buffers (CUDA IPC) and PUSHES its column block's rows into them with peer cudaMemcpyAsync over NVLink -- no SM is used, whereas
+    // NCCL's send/recv kernels took ~3 % of the leaf hashing they run under (profiles/r2_33, r2_34).  A one-word ncclAllGather is the barrier.
+    int ce_mode = 1;          // 0: NCCL send/recv, 1: copy engines when every rank could map every peer
+    bool ce_ok = false;       // outcome of the last mapping round (the same on every rank)
+    bool ce_used = false;     // the last commit went through the copy engines
+    u64 *ipc_dev = nullptr;   // device staging: kMaxPanels records of kIpcWords words, then the barrier words
+    struct Peer {
+        u64 rec[10] = {0};    // last record seen from this rank: 64-byte cudaIpcMemHandle_t, byte offset of row_panels in its allocation, valid flag
+        void *base = nullptr; // mapping of the peer's allocation in this process (cudaIpcOpenMemHandle)
+    } peer[8];
 } nc;
+constexpr int kIpcWords = 10;
 
 #define NC(call)                                                                                                 \
     do {                                                                                                         \
@@ -1490,15 +1502,112 @@ int gl_fill_synthetic_dev(uint64_t *dst, uint64_t words, uint64_t seed, uint64_t
 } // extern "C" (closed for the helper below)
 
 namespace {
+// base address of the cudaMalloc allocation that contains `ptr` (cuMemGetAddressRange through the runtime's driver entry point: the
+// library links cudart only).  An IPC handle always names a whole allocation; the caller's row_panels may sit inside one.
+bool alloc_base(const void *ptr, void **base)
+{
+    typedef int (*RangeFn)(unsigned long long *, size_t *, unsigned long long);
+    static RangeFn fn = nullptr;
+    if (!fn) {
+        void *q = nullptr;
+        cudaDriverEntryPointQueryResult r;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &q, cudaEnableDefault, &r) != cudaSuccess || r != cudaDriverEntryPointSuccess) return false;
+        fn = (RangeFn)q;
+    }
+    unsigned long long b = 0;
+    size_t sz = 0;
+    if (fn(&b, &sz, (unsigned long long)(uintptr_t)ptr) != 0) return false;
+    *base = (void *)(uintptr_t)b;
+    return true;
+}
+
+// one-word all-gather on the exchange stream: completes on a rank only after every rank's stream has reached it
+int mgpu_barrier()
+{
+    u64 *bar = nc.ipc_dev + (size_t)poseidon::kMaxPanels * kIpcWords;
+    NC(nc.AllGather(bar + nc.rank, bar, 1, ncclUint64, nc.comm, g.s_comm));
+    return GL_OK;
+}
+
+// Collective (every rank calls it at the start of every multi-GPU commit): tell the peers where this rank's row_panels buffer is and
+// map theirs.  Steady state = one 80-byte all-gather and one stream synchronisation (~30 us); the mappings are redone only when some
+// rank's record changed.  All ranks see the same records, so all take the same branches; when any rank cannot export or map a
+// buffer every rank falls back to the NCCL exchange.
+int mgpu_map_peers(const u64 *row_panels, bool *use_ce)
+{
+    *use_ce = false;
+    const int G = nc.world, me = nc.rank;
+    if (G == 1 || nc.ce_mode == 0) return GL_OK;
+    u64 all[poseidon::kMaxPanels * kIpcWords], mine[kIpcWords];
+    memset(mine, 0, sizeof mine);
+    {
+        void *base = nullptr;
+        cudaIpcMemHandle_t h;
+        static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t size");
+        if (alloc_base(row_panels, &base) && cudaIpcGetMemHandle(&h, base) == cudaSuccess) {
+            memcpy(mine, &h, 64);
+            mine[8] = (u64)((const char *)row_panels - (const char *)base);
+            mine[9] = 1;
+        } else {
+            cudaGetLastError();
+        }
+    }
+    CU(cudaMemcpyAsync(nc.ipc_dev + (size_t)me * kIpcWords, mine, sizeof mine, cudaMemcpyHostToDevice, g.s_comm));
+    NC(nc.AllGather(nc.ipc_dev + (size_t)me * kIpcWords, nc.ipc_dev, kIpcWords, ncclUint64, nc.comm, g.s_comm));
+    CU(cudaMemcpyAsync(all, nc.ipc_dev, (size_t)G * kIpcWords * 8, cudaMemcpyDeviceToHost, g.s_comm));
+    CU(cudaStreamSynchronize(g.s_comm));
+    bool changed = false, exported = true;
+    for (int p = 0; p < G; p++) {
+        if (memcmp(all + p * kIpcWords, nc.peer[p].rec, sizeof mine) != 0) changed = true;
+        if (all[p * kIpcWords + 9] != 1) exported = false;
+    }
+    if (changed) {
+        u64 ok = exported ? 1 : 0;
+        for (int p = 0; p < G; p++) {
+            const bool differs = memcmp(all + p * kIpcWords, nc.peer[p].rec, sizeof mine) != 0;
+            memcpy(nc.peer[p].rec, all + p * kIpcWords, sizeof mine);
+            if (p == me || !differs) continue;
+            if (nc.peer[p].base) {
+                cudaStreamSynchronize(g.stream); // nothing of an earlier commit still writes through the old mapping
+                cudaIpcCloseMemHandle(nc.peer[p].base);
+                nc.peer[p].base = nullptr;
+            }
+            if (!exported) continue;
+            cudaIpcMemHandle_t h;
+            memcpy(&h, all + p * kIpcWords, 64);
+            if (cudaIpcOpenMemHandle(&nc.peer[p].base, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                cudaGetLastError();
+                nc.peer[p].base = nullptr;
+                ok = 0;
+            }
+        }
+        // second round: did every rank map every peer?
+        u64 *flags = nc.ipc_dev + (size_t)poseidon::kMaxPanels * kIpcWords + poseidon::kMaxPanels;
+        u64 oks[poseidon::kMaxPanels];
+        CU(cudaMemcpyAsync(flags + me, &ok, 8, cudaMemcpyHostToDevice, g.s_comm));
+        NC(nc.AllGather(flags + me, flags, 1, ncclUint64, nc.comm, g.s_comm));
+        CU(cudaMemcpyAsync(oks, flags, (size_t)G * 8, cudaMemcpyDeviceToHost, g.s_comm));
+        CU(cudaStreamSynchronize(g.s_comm));
+        nc.ce_ok = true;
+        for (int p = 0; p < G; p++)
+            if (oks[p] != 1) nc.ce_ok = false;
+    }
+    *use_ce = nc.ce_ok;
+    return GL_OK;
+}
+
+u64 *peer_panels(int p) { return (u64 *)((char *)nc.peer[p].base + nc.peer[p].rec[8]); }
+
 // Exchange + leaf hashing of the multi-GPU commit, in row chunks: chunk j of this rank's rows is exchanged on the
 // communication stream (grouped ncclSend/ncclRecv: rows [h*rows + r0, +rc) of my column block go to rank h; I receive
 // rank p's columns of my rows r0..r0+rc into panel p) while chunk j-1 is being hashed on the compute stream, so only the
 // first chunk's transfer is exposed.  Both sides of every message are contiguous (the column block and the panels are
 // row-major), so chunking needs no re-pack.  With row_panels_host the received chunk also starts its way to the host.
 // Records g.ev[1] when the first chunk has arrived and g.ev[2] after the last leaf kernel.
-int mgpu_exchange_and_hash(const u64 *lde_cols, u64 *row_panels, u64 *subtree, u64 rows, u64 w, u64 ncols_total, u64 *row_panels_host)
+int mgpu_exchange_and_hash(const u64 *lde_cols, u64 *row_panels, u64 *subtree, u64 rows, u64 w, u64 ncols_total, u64 *row_panels_host, bool ce)
 {
     const int G = nc.world, me = nc.rank;
+    nc.ce_used = ce;
     poseidon::RowPanels rp = {};
     rp.npanels = (u32)G;
     for (int p = 0; p <= G; p++) rp.start[p] = (u32)col_start(ncols_total, G, p);
@@ -1524,16 +1633,29 @@ int mgpu_exchange_and_hash(const u64 *lde_cols, u64 *row_panels, u64 *subtree, u
     }
     CU(cudaEventRecord(g.ev[5], g.stream));
     CU(cudaStreamWaitEvent(g.s_comm, g.ev[5], 0)); // the column block is complete
+    // copy engines: every rank has finished its LDE -- and with it, in stream order, the hashing of its previous commit -- before
+    // anyone writes into its panels
+    if (ce) TRY(mgpu_barrier());
     for (u64 j = 0; j < J; j++) {
         const u64 r0 = bounds[j], rc = bounds[j + 1] - bounds[j];
-        NC(nc.GroupStart());
-        for (int p = 0; p < G; p++) {
-            if (p == me) continue;
-            const u64 wp = rp.start[p + 1] - rp.start[p];
-            if (w) NC(nc.Send(lde_cols + ((u64)p * rows + r0) * w, rc * w, ncclUint64, p, nc.comm, g.s_comm));
-            if (wp) NC(nc.Recv((void *)(rp.base[p] + r0 * wp), rc * wp, ncclUint64, p, nc.comm, g.s_comm));
+        if (ce) {
+            // push rows [p * rows + r0, + rc) of my column block into panel `me` of rank p (both sides contiguous), then the barrier:
+            // when it completes here, every peer's pushes of this chunk -- ordered before its barrier on its stream -- have landed
+            for (int q = 1; q < G && w; q++) {
+                const int p = (me + q) % G; // staggered: at any moment the ranks write to different peers
+                CU(cudaMemcpyAsync(peer_panels(p) + rows * rp.start[me] + r0 * w, lde_cols + ((u64)p * rows + r0) * w, rc * w * 8, cudaMemcpyDeviceToDevice, g.s_comm));
+            }
+            TRY(mgpu_barrier());
+        } else {
+            NC(nc.GroupStart());
+            for (int p = 0; p < G; p++) {
+                if (p == me) continue;
+                const u64 wp = rp.start[p + 1] - rp.start[p];
+                if (w) NC(nc.Send(lde_cols + ((u64)p * rows + r0) * w, rc * w, ncclUint64, p, nc.comm, g.s_comm));
+                if (wp) NC(nc.Recv((void *)(rp.base[p] + r0 * wp), rc * wp, ncclUint64, p, nc.comm, g.s_comm));
+            }
+            NC(nc.GroupEnd());
         }
-        NC(nc.GroupEnd());
         if (w) CU(cudaMemcpyAsync((void *)(rp.base[me] + r0 * w), lde_cols + ((u64)me * rows + r0) * w, rc * w * 8, cudaMemcpyDeviceToDevice, g.s_comm));
         CU(cudaEventRecord(g.ev_chunk[j], g.s_comm));
         CU(cudaStreamWaitEvent(g.stream, g.ev_chunk[j], 0));
@@ -1583,8 +1705,16 @@ int gl_mgpu_init(const uint8_t id[128], int rank, int world)
     nc.rank = rank;
     nc.world = world;
     CU(cudaMalloc(&nc.top, gl_tree_num_elements(world) * 8));
+    CU(cudaMalloc(&nc.ipc_dev, ((size_t)poseidon::kMaxPanels * kIpcWords + 2 * poseidon::kMaxPanels) * 8));
+    CU(cudaMemset(nc.ipc_dev, 0, ((size_t)poseidon::kMaxPanels * kIpcWords + 2 * poseidon::kMaxPanels) * 8));
+    nc.ce_mode = 1;
+    if (const char *v = getenv("GLB_MGPU_EXCHANGE")) nc.ce_mode = strcmp(v, "nccl") == 0 ? 0 : 1;
+    nc.ce_ok = nc.ce_used = false;
+    for (auto &pr : nc.peer) pr = Nccl::Peer();
     return GL_OK;
 }
+
+int gl_mgpu_exchange_mode(void) { return nc.ce_used ? 1 : 0; }
 
 int gl_mgpu_shutdown(void)
 {
@@ -1594,6 +1724,13 @@ int gl_mgpu_shutdown(void)
         nc.CommDestroy(nc.comm);
         nc.comm = nullptr;
     }
+    for (auto &pr : nc.peer) {
+        if (pr.base) cudaIpcCloseMemHandle(pr.base);
+        pr = Nccl::Peer();
+    }
+    if (nc.ipc_dev) cudaFree(nc.ipc_dev);
+    nc.ipc_dev = nullptr;
+    nc.ce_ok = nc.ce_used = false;
     if (nc.top) cudaFree(nc.top);
     nc.top = nullptr;
     nc.rank = 0;
@@ -1613,12 +1750,14 @@ int gl_commit_mgpu(uint64_t *lde_cols, uint64_t *row_panels, uint64_t *subtree, 
     if (n_ext < (u64)G) return fail(GL_ERR_ARG, "commit: %llu extended rows cannot be split over %d ranks", (u64)n_ext, G);
     const u64 rows = n_ext / G;
     const u64 c0 = col_start(ncols_total, G, me), w = col_start(ncols_total, G, me + 1) - c0;
+    bool use_ce = false;
+    TRY(mgpu_map_peers((const u64 *)row_panels, &use_ce));
 
     CU(cudaEventRecord(g.ev[0], g.stream));
     TRY(extend_pol_dev((u64 *)lde_cols, (const u64 *)in_cols, n_ext, n, w));
     CU(cudaEventRecord(g.ev[4], g.stream));
 
-    TRY(mgpu_exchange_and_hash((const u64 *)lde_cols, (u64 *)row_panels, (u64 *)subtree, rows, w, ncols_total, nullptr));
+    TRY(mgpu_exchange_and_hash((const u64 *)lde_cols, (u64 *)row_panels, (u64 *)subtree, rows, w, ncols_total, nullptr, use_ce));
     g.launches += poseidon::launch_tree_levels((u64 *)subtree, rows, g.stream);
     CU(cudaGetLastError());
     TRY(mgpu_top((const u64 *)subtree + gl_tree_num_elements(rows) - 4, root));
@@ -1646,6 +1785,8 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
     const u64 rows = n_ext / G;
     const u64 c0r = col_start(ncols_total, G, me), w = col_start(ncols_total, G, me + 1) - c0r;
     const u32 logn = ilog2(n), loge = ilog2(n_ext);
+    bool use_ce = false;
+    TRY(mgpu_map_peers((const u64 *)row_panels, &use_ce));
 
     CU(cudaEventRecord(g.ev[0], g.stream));
     DevBuf stage;
@@ -1691,7 +1832,7 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
     }
     CU(cudaEventRecord(g.ev[4], g.stream));
 
-    TRY(mgpu_exchange_and_hash((const u64 *)lde_cols, (u64 *)row_panels, (u64 *)subtree, rows, w, ncols_total, (u64 *)row_panels_host));
+    TRY(mgpu_exchange_and_hash((const u64 *)lde_cols, (u64 *)row_panels, (u64 *)subtree, rows, w, ncols_total, (u64 *)row_panels_host, use_ce));
     g.launches += poseidon::launch_tree_levels((u64 *)subtree, rows, g.stream);
     CU(cudaGetLastError());
     TRY(mgpu_top((const u64 *)subtree + gl_tree_num_elements(rows) - 4, root));

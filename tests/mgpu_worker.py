@@ -133,6 +133,8 @@ def main():
             dfull = glb.DeviceBuffer(glb.tree_num_elements(e))
             root = glb.commit_mgpu(dlde.ptr, dpan.ptr, dsub.ptr, din.ptr, e, n, ncols)
             assert np.array_equal(root, tree_full[-4:]), "root differs (%d,%d,%d)" % (n, e, ncols)
+            # default transport: peer copies over NVLink through the copy engines (CUDA IPC mappings of the peers' panels)
+            assert glb.lib().gl_mgpu_exchange_mode() == (1 if world > 1 and os.environ.get("GLB_MGPU_EXCHANGE") != "nccl" else 0), "exchange fell back to NCCL send/recv"
             assert np.array_equal(dlde.download(e * w).reshape(e, w), lde_full[:, c0:c1])
             pan = dpan.download(rows * ncols)
             for p, (off, pw) in enumerate(sp.panel_offsets(e, ncols, world)):
@@ -153,6 +155,34 @@ def main():
             assert np.array_equal(hpan[:rows * ncols], pan), "host-pointer panels differ"
             assert np.array_equal(hsub, sub_dev), "host-pointer subtree differs"
         dist.barrier()
+    if mode == "nccl" and world > 1 and os.environ.get("GLB_MGPU_EXCHANGE") != "nccl":
+        # the other transport (grouped ncclSend/ncclRecv, what a rank falls back to when a buffer cannot be mapped): new communicator
+        glb.mgpu_shutdown()
+        os.environ["GLB_MGPU_EXCHANGE"] = "nccl"
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(glb.mgpu_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        glb.mgpu_init(idt.cpu().numpy().tobytes(), rank, world)
+        for (n, e, ncols) in SHAPES[:2]:
+            x, _ = o.xorshift(n * ncols)
+            x = x.reshape(n, ncols)
+            tree_full = o.merkletree(o.extend_pol(x, e))
+            c0, c1 = sp.col_range(ncols, world, rank)
+            w, rows = c1 - c0, e // world
+            din = glb.DeviceBuffer(max(1, n * w)).upload(np.ascontiguousarray(x[:, c0:c1]))
+            dlde, dpan, dsub = glb.DeviceBuffer(max(1, e * w)), glb.DeviceBuffer(max(1, rows * ncols)), glb.DeviceBuffer(glb.tree_num_elements(rows))
+            root = glb.commit_mgpu(dlde.ptr, dpan.ptr, dsub.ptr, din.ptr, e, n, ncols)
+            assert glb.lib().gl_mgpu_exchange_mode() == 0
+            assert np.array_equal(root, tree_full[-4:]), "NCCL-exchange root differs (%d,%d,%d)" % (n, e, ncols)
+        dist.barrier()
+        glb.mgpu_shutdown()
+        os.environ.pop("GLB_MGPU_EXCHANGE")
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(glb.mgpu_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        glb.mgpu_init(idt.cpu().numpy().tobytes(), rank, world)
     os.environ.pop("GLB_MGPU_WAVE_ROWS", None)
     if mode == "nccl" and os.environ.get("GLB_MGPU_FULL") == "1":
         full_size_check(glb, o, rank, world)
