@@ -206,7 +206,8 @@ int gl_last_timings4(float ms[4]);
 
 /* ---- multi-GPU: one process per GPU (the reference is single-process OpenMP and has no
  *      counterpart).  Columns are split over ranks for extendPol (ntt_goldilocks.cpp:326-352 is
- *      column-independent), an NCCL all-to-all over NVLink turns column blocks into row blocks, each
+ *      column-independent), an all-to-all over NVLink (peer copies through the copy engines into CUDA-IPC mappings of the
+ *      peers' row_panels; grouped ncclSend/ncclRecv as the fallback) turns column blocks into row blocks, each
  *      rank hashes its E/world rows (poseidon_goldilocks.cpp:277-281) and builds its subtree
  *      (:283-300); the world subtree roots are gathered and the top log2(world) levels hashed on every
  *      rank.  Result: the same root and node values as the single-GPU call.
