@@ -107,6 +107,42 @@ __device__ __forceinline__ u64 reduce96(u32 x0, u32 x1, u32 x2)
     return pack(r0, r1);
 }
 
+// reduce96 with ONE IMAD.WIDE: the conditional + (2^32 - 1) of the second step as mask arithmetic instead of a second multiply-add.
+// FORM 1: k -> mask with a sign extension of bit 0 (bfe.s32: ALU pipe), add.cc, addc.  FORM 2: {r0 - k, r1 + k - borrow}.
+// A/B switch for the MDS folds of the Poseidon layers (GLB_POSEIDON_FOLD); same value as reduce96 for every input.
+template <int FORM>
+__device__ __forceinline__ u64 reduce96_one(u32 x0, u32 x1, u32 x2)
+{
+    u32 r0, r1;
+    if (FORM == 1) {
+        asm("{\n\t"
+            ".reg .u32 k, m;\n\t"
+            "mad.lo.cc.u32 %0, %4, %5, %2;\n\t"
+            "madc.hi.cc.u32 %1, %4, %5, %3;\n\t"
+            "addc.u32 k, 0, 0;\n\t"
+            "bfe.s32 m, k, 0, 1;\n\t"                 // 0 or 0xFFFFFFFF
+            "add.cc.u32 %0, %0, m;\n\t"
+            "addc.u32 %1, %1, 0;\n\t"
+            "}"
+            : "=&r"(r0), "=&r"(r1)
+            : "r"(x0), "r"(x1), "r"(x2), "r"(c_eps[0]));
+    } else {
+        asm("{\n\t"
+            ".reg .u32 k, b;\n\t"
+            "mad.lo.cc.u32 %0, %4, %5, %2;\n\t"
+            "madc.hi.cc.u32 %1, %4, %5, %3;\n\t"
+            "addc.u32 k, 0, 0;\n\t"
+            "sub.cc.u32 %0, %0, k;\n\t"
+            "subc.u32 b, 0, 0;\n\t"                   // -borrow
+            "add.u32 %1, %1, k;\n\t"
+            "add.u32 %1, %1, b;\n\t"
+            "}"
+            : "=&r"(r0), "=&r"(r1)
+            : "r"(x0), "r"(x1), "r"(x2), "r"(c_eps[0]));
+    }
+    return pack(r0, r1);
+}
+
 // 160-bit input x0 + x1 2^32 + x2 2^64 + x3 2^96 + x4 2^128 with x4 < 2^31 (2^128 = -2^32 mod p):
 //   {x0,x1} - {x3,x4} + x2*(2^32-1); same single net correction as reduce128.
 __device__ __forceinline__ u64 reduce160(u32 x0, u32 x1, u32 x2, u32 x3, u32 x4)

@@ -67,9 +67,24 @@ __device__ __forceinline__ u64 sbox_add(u64 x, u64 c)
     return gl::mad(x3, x4, c);
 #endif
 }
+#ifndef GLB_POSEIDON_FOLD
+#define GLB_POSEIDON_FOLD 1 // 1 / 2: the 96-bit reduction of the MDS folds with one IMAD.WIDE instead of two (gl::reduce96_one<1 / 2>); 0: gl::reduce96
+#endif
+// Three places that spent an IMAD.WIDE (4 issue clocks, nothing beside it) on a conditional +-(2^32 - 1): the second step of the MDS
+// folds (GLB_POSEIDON_FOLD), the canonicalisation inside mds_pair's y - x (GLB_POSEIDON_SUB_SEL) and the 12 additions of the
+// pre-round constants (GLB_POSEIDON_RC0_CX).  Leaf kernel on 2^20 x 600: 1601.5 -> 1613.9 (fold) -> 1621.2 M perm/s (all three),
+// profiles/r2_37_leaf_wide_saving_ab.txt; 0 restores the round-1 forms for A/B builds.
+#ifndef GLB_POSEIDON_SUB_SEL
+#define GLB_POSEIDON_SUB_SEL 1
+#endif
+#ifndef GLB_POSEIDON_RC0_CX
+#define GLB_POSEIDON_RC0_CX 1
+#endif
 __device__ __forceinline__ u64 red96(u32 x0, u32 x1, u32 x2)
 {
-#if GLB_POSEIDON_RED_ALU >= 2
+#if GLB_POSEIDON_FOLD
+    return gl::reduce96_one<GLB_POSEIDON_FOLD>(x0, x1, x2);
+#elif GLB_POSEIDON_RED_ALU >= 2
     return gl::reduce96_alu(x0, x1, x2);
 #else
     return gl::reduce96(x0, x1, x2);
@@ -316,7 +331,11 @@ __device__ __forceinline__ void mds_pair(u64 (&s)[12], u64 c_next)
         x = red96((u32)L, (u32)t, (u32)(t >> 32));
     }
     const u64 y = sbox_add(x, c_next);
+#if defined(GLB_POSEIDON_SUB_SEL) && GLB_POSEIDON_SUB_SEL
+    const u64 d = gl::sub_c(y, gl::canon_sel(x)); // canonicalisation without an IMAD.WIDE
+#else
     const u64 d = gl::sub(y, x);
+#endif
     const double dlo = u32_to_f64((u32)d), dhi = u32_to_f64((u32)(d >> 32));
 #if GLB_MDS_SPLIT >= 2
     {
@@ -409,7 +428,11 @@ template <bool OUT4 = false>
 __device__ __forceinline__ void permute(u64 (&s)[12])
 {
 #pragma unroll
+#if defined(GLB_POSEIDON_RC0_CX) && GLB_POSEIDON_RC0_CX
+    for (int i = 0; i < 12; i++) s[i] = gl::add_cx(s[i], c_RC0[i]); // the IMAD.WIDE-free addition of the NTT butterflies (constants are canonical)
+#else
     for (int i = 0; i < 12; i++) s[i] = gl::add_c(s[i], c_RC0[i]);
+#endif
     // 19 stages, one loop body: stages 0..3 and 15..18 are full rounds (S-box on all 12 words, MDS layer), stages 4..14
     // are PAIRS of partial rounds (mds_pair)
 #pragma unroll 1

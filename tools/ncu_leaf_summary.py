@@ -1,6 +1,7 @@
 """Distil an `ncu --set full --import-source on` capture of the leaf kernel (exported with `ncu -i X.ncu-rep --page raw --csv`
 and `--page source --csv`) into the text summary kept under profiles/.
-usage: python tools/ncu_leaf_summary.py RAW.csv SOURCE.csv "header line" LOG_ROWS PERMS_PER_ROW > profiles/...txt"""
+usage: python tools/ncu_leaf_summary.py RAW.csv SOURCE.csv "header line" LOG_ROWS PERMS_PER_ROW [MIX.json] > profiles/...txt
+With MIX.json the per-class counts per permutation (the classes of tools/sass_cost.py) are also written there for bench.py."""
 import collections
 import csv
 import re
@@ -37,3 +38,26 @@ wp = (1 << log_rows) * perms / 32
 print("per-opcode warp instructions per permutation (source page, 2^%d rows x %d permutations): total %.0f" % (log_rows, perms, tot / wp))
 for k, n in c.most_common(20):
     print("  %-22s %8.1f" % (k, n / wp))
+
+if len(sys.argv) > 6:
+    import json
+    cls = dict(imad_wide=0.0, imad_other=0.0, fp64=0.0, alu=0.0, i2f=0.0)
+    for k, n in c.items():
+        b = k.split(".")[0]
+        if k.startswith(("IMAD.WIDE", "IMAD.HI")):
+            cls["imad_wide"] += n / wp
+        elif k.startswith("IMAD"):
+            cls["imad_other"] += n / wp
+        elif b in ("DFMA", "DADD", "DMUL"):
+            cls["fp64"] += n / wp
+        elif b in ("IADD3", "LOP3", "SHF", "SEL", "LEA", "ISETP", "PRMT", "MOV", "VIADD", "PLOP3", "IABS", "FSEL", "SGXT"):
+            cls["alu"] += n / wp
+        elif b in ("I2F", "F2I"):
+            cls["i2f"] += n / wp
+    rd, wr = float(d["dram__bytes_read.sum"][0].replace(",", "")), float(d["dram__bytes_write.sum"][0].replace(",", ""))
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    rd *= unit.get(d["dram__bytes_read.sum"][1], 1.0)
+    wr *= unit.get(d["dram__bytes_write.sum"][1], 1.0)
+    algo = (1 << log_rows) * (perms * 8 * 8 + 32)
+    out = dict(source=header, warp_instr_per_perm=tot / wp, dram_bytes_per_algorithmic_byte=(rd + wr) / algo, **cls)
+    json.dump(out, open(sys.argv[6], "w"), indent=1)
