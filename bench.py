@@ -151,7 +151,7 @@ def leaf_roofline(glb, leaf_perm, leaf_ms, leaf_share, leaf_bytes, clocks, hbm_p
                                "formula": "T = c_w*WIDE + max(c_a*IMADother + c_d*FP64, c_a*ALU, 4*c_a*I2F) clocks per warp permutation"},
                 "imad": {"achieved_lane_ops_per_s": imad_algo, "peak_lane_ops_per_s": pk["imad_wide_lane_ops_per_s"], "frac": imad_algo / pk["imad_wide_lane_ops_per_s"],
                          "note": "SURVEY 8(d) accounting of the reference algorithm (1144 modmul x 5 + 1008 MAC x 2 IMAD-class lane-ops per permutation) against the measured real "
-                                 "IMAD.WIDE.U32 rate; above 1 because the dense-form kernel executes 2609 IMAD.WIDE per permutation, not 5720"},
+                                 "IMAD.WIDE.U32 rate; above 1 because the dense-form kernel executes %.0f IMAD.WIDE per permutation, not 5720" % mix["imad_wide"]},
                 "hbm": {"achieved": leaf_bytes / (leaf_ms / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": leaf_bytes / (leaf_ms / 1e3) / 1e9 / hbm_peak,
                         "peak_source": peak_src},
                 "traffic": leaf_bytes * mix["dram_bytes_per_algorithmic_byte"],
