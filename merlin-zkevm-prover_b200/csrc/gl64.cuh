@@ -323,9 +323,24 @@ __device__ __forceinline__ u64 canon(u64 x)
 // instructions per 8 products), so gl::mul and mul_pow2 stay as they are.  gl_field_op_host ops 7-9 check the values.
 
 // x mod p:  x >= p  <=>  x + (2^32 - 1) carries; then x - p = x + (2^32 - 1) - 2^64.          ALU 3, IMAD 3, no IMAD.WIDE
+#ifndef GLB_CANON_SEL2
+#define GLB_CANON_SEL2 1 // 1: no second carry chain (x >= p implies hi = 2^32 - 1 and lo >= 1, so x - p = {lo - 1, hi + 1 = 0}): ALU 2, IMAD 3
+#endif
 __device__ __forceinline__ u64 canon_sel(u64 x)
 {
     u32 r0, r1;
+#if GLB_CANON_SEL2
+    asm("{\n\t"
+        ".reg .u32 t, k;\n\t"
+        "add.cc.u32 t, %2, 0xFFFFFFFF;\n\t"
+        "addc.cc.u32 t, %3, 0;\n\t"
+        "madc.lo.u32 k, 0, 0, 0;\n\t"               // k = carry = (x >= p)
+        "mad.lo.u32 %0, k, 0xFFFFFFFF, %2;\n\t"     // lo - k   (lo >= 1 when k = 1: no borrow)
+        "mad.lo.u32 %1, k, 1, %3;\n\t"              // hi + k   (hi = 2^32 - 1 when k = 1: wraps to 0)
+        "}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"((u32)x), "r"((u32)(x >> 32)));
+#else
     asm("{\n\t"
         ".reg .u32 t, k, m;\n\t"
         "add.cc.u32 t, %2, 0xFFFFFFFF;\n\t"
@@ -337,6 +352,7 @@ __device__ __forceinline__ u64 canon_sel(u64 x)
         "}"
         : "=&r"(r0), "=&r"(r1)
         : "r"((u32)x), "r"((u32)(x >> 32)));
+#endif
     return pack(r0, r1);
 }
 // a + b, b canonical:  s + carry * (2^32 - 1) = {s1, s0 + m} with m = -carry and the carry of the low word into s1.   ALU 3, IMAD 3
