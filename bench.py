@@ -48,8 +48,8 @@ def leaf_mix():
         with open(os.path.join(ROOT, "profiles", "r2_leaf_instr_mix.json")) as f:
             return json.load(f)
     except Exception:
-        return {"source": "fallback: profiles/r2_38_leaf_ncu_shipped.txt", "warp_instr_per_perm": 14228.0, "imad_wide": 2355.0, "imad_other": 1985.0,
-                "fp64": 3802.0, "alu": 5140.0, "i2f": 500.0, "dram_bytes_per_algorithmic_byte": 1.003}
+        return {"source": "fallback: profiles/r2_42_leaf_ncu_shipped.txt", "warp_instr_per_perm": 13858.0, "imad_wide": 2355.0, "imad_other": 1974.0,
+                "fp64": 3802.0, "alu": 4808.0, "i2f": 500.0, "dram_bytes_per_algorithmic_byte": 1.003}
 
 
 def peaks():

@@ -230,21 +230,27 @@ __device__ __forceinline__ u64 sqr(u64 a) { return reduce128(mul_wide_native(a, 
 // (GLB_POSEIDON_SQR3); tests/test_gpu_parity.py::test_field_ops checks the value as op "sqr3".
 __device__ __forceinline__ u64 sqr3(u64 a)
 {
-    const u32 a0 = (u32)a, a1 = (u32)(a >> 32);
-    const u64 p0 = (u64)a0 * a0, p2 = (u64)a1 * a1, c = (u64)a0 * a1;
+    // all in one asm block: with the three products formed in C and their halves passed in as separate operands, ptxas
+    // materialised every extracted half with an addition of a zero uniform register (three no-op VIADD / IADD3 per squaring)
     u128 r;
     asm("{\n\t"
-        ".reg .u32 d0, d1, d2;\n\t"
-        "shl.b32 d0, %6, 1;\n\t"
-        "shf.l.wrap.b32 d1, %6, %7, 1;\n\t"
-        "shr.b32 d2, %7, 31;\n\t"
-        "add.cc.u32 %1, %4, d0;\n\t"
-        "addc.cc.u32 %2, %5, d1;\n\t"
-        "addc.u32 %3, %8, d2;\n\t"
-        "mov.u32 %0, %9;\n\t"
+        ".reg .u64 p0, p2, c;\n\t"
+        ".reg .u32 p0h, p2l, p2h, cl, ch, d0, d1, d2;\n\t"
+        "mul.wide.u32 p0, %4, %4;\n\t"
+        "mul.wide.u32 c, %4, %5;\n\t"
+        "mul.wide.u32 p2, %5, %5;\n\t"
+        "mov.b64 {%0, p0h}, p0;\n\t"
+        "mov.b64 {cl, ch}, c;\n\t"
+        "mov.b64 {p2l, p2h}, p2;\n\t"
+        "shl.b32 d0, cl, 1;\n\t"
+        "shf.l.wrap.b32 d1, cl, ch, 1;\n\t"
+        "shr.b32 d2, ch, 31;\n\t"
+        "add.cc.u32 %1, p0h, d0;\n\t"
+        "addc.cc.u32 %2, p2l, d1;\n\t"
+        "addc.u32 %3, p2h, d2;\n\t"
         "}"
         : "=r"(r.x0), "=r"(r.x1), "=r"(r.x2), "=r"(r.x3)
-        : "r"((u32)(p0 >> 32)), "r"((u32)p2), "r"((u32)c), "r"((u32)(c >> 32)), "r"((u32)(p2 >> 32)), "r"((u32)p0));
+        : "r"((u32)a), "r"((u32)(a >> 32)));
     return reduce128(r);
 }
 // a*b + c  (fused: the addend rides on the first partial product)

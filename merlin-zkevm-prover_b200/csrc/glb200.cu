@@ -274,23 +274,30 @@ int ensure_rscale(u32 logn)
     return GL_OK;
 }
 
-template <int B2, bool LAST, int CW, bool BIG>
-int launch_pass_inst(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
+template <int B2, bool LAST, int CW, bool BIG, bool PAD>
+int launch_pass_pad(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
 {
     constexpr int R = 16 << B2;
     size_t smem = B2 > 0 ? (size_t)R * ntt::kTileCols * 8 : 0;
     static bool attr_done[16] = {false}; // per device: the attribute belongs to the device's copy of the function
     if (!attr_done[g.device & 15] && smem > 48 * 1024) {
-        CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST, CW, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CU(cudaFuncSetAttribute(ntt::k_pass<B2, LAST, CW, BIG, PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_done[g.device & 15] = true;
     }
     dim3 grid((unsigned)(ntiles / (ntt::kTileCols / CW)), coltiles), block(32, 1 << B2);
     ntt::PassParams q = p;
     q.pf_dist = (u32)(g.ntt_prefetch * g.sms * (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))); // resident CTAs per SM as in __launch_bounds__
-    ntt::k_pass<B2, LAST, CW, BIG><<<grid, block, smem, g.stream>>>(q);
+    ntt::k_pass<B2, LAST, CW, BIG, PAD><<<grid, block, smem, g.stream>>>(q);
     g.launches++;
     CU(cudaGetLastError());
     return GL_OK;
+}
+template <int B2, bool LAST, int CW, bool BIG>
+int launch_pass_inst(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
+{
+    // only the first pass of an extended forward transform reads a zero-padded source; every other pass skips the validity tests
+    if (p.nvalid < (1ULL << p.logn)) return launch_pass_pad<B2, LAST, CW, BIG, true>(p, ntiles, coltiles);
+    return launch_pass_pad<B2, LAST, CW, BIG, false>(p, ntiles, coltiles);
 }
 template <int B2, bool LAST, int CW>
 int launch_pass_cw(const ntt::PassParams &p, u64 ntiles, u32 coltiles)

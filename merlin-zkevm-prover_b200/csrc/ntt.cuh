@@ -158,7 +158,10 @@ template <int B2, bool CSEL = false> struct Step2 {
 //   lane groups (per-lane instead of warp-uniform), everything that depends only on threadIdx.y stays uniform.
 // BIG: two-level twiddle lookup / on-the-fly extend scale of the domains above 2^27 -- a separate instantiation, so that the kernel of
 // the ordinary domains carries no second copy of its store loop (it cost 6 % of the c2 LDE as a run-time branch: instruction cache).
-template <int B2, bool LAST, int CW = kTileCols, bool BIG = false>
+// PAD: the source may be zero padded (rows >= nvalid read as zeros: the first pass of the extended forward transform).  Every other
+// pass is launched with PAD = false and carries no per-row validity tests (16 ISETP + 16 selects per thread on the ALU pipe, which
+// bounds the pass).
+template <int B2, bool LAST, int CW = kTileCols, bool BIG = false, bool PAD = true>
 __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k_pass(const PassParams p)
 {
     constexpr int R2 = 1 << B2;
@@ -177,10 +180,13 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
     {
         const u64 row0 = base_in + ((u64)t << p.log_rest);
         const u32 rshift = p.log_rest + B2; // rstep = R2 << log_rest
-        u32 iv = 0;
-        if (colok && p.nvalid > row0) {
-            const u64 q = ((p.nvalid - row0 - 1) >> rshift) + 1;
-            iv = q < 16 ? (u32)q : 16u;
+        u32 iv = colok ? 16u : 0u;
+        if (PAD) {
+            iv = 0;
+            if (colok && p.nvalid > row0) {
+                const u64 q = ((p.nvalid - row0 - 1) >> rshift) + 1;
+                iv = q < 16 ? (u32)q : 16u;
+            }
         }
         const u64 *sp = p.src + row0 * p.spitch + col;
         const u64 sstep = p.spitch << rshift;
@@ -193,10 +199,13 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
             const u64 tau2 = tau + p.pf_dist;
             if (tau2 < gridDim.x) {
                 const u64 row2 = ((((tau2 >> p.log_rest) * R) << p.log_rest) + (tau2 & ((1ULL << p.log_rest) - 1))) + ((u64)t << p.log_rest);
-                u32 iv2 = 0;
-                if (p.nvalid > row2) {
-                    const u64 q = ((p.nvalid - row2 - 1) >> rshift) + 1;
-                    iv2 = q < 16 ? (u32)q : 16u;
+                u32 iv2 = 16u;
+                if (PAD) {
+                    iv2 = 0;
+                    if (p.nvalid > row2) {
+                        const u64 q = ((p.nvalid - row2 - 1) >> rshift) + 1;
+                        iv2 = q < 16 ? (u32)q : 16u;
+                    }
                 }
                 const u64 *pp = p.src + row2 * p.spitch + col;
 #pragma unroll
