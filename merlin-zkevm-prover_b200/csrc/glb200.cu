@@ -12,6 +12,7 @@
 #include <dlfcn.h>
 #include <nccl.h> // types and prototypes only: libnccl.so.2 is dlopen'ed by gl_mgpu_init (single-GPU users need no NCCL)
 
+#include <algorithm>
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
@@ -890,9 +891,11 @@ int commit_host_pipelined(uint64_t *lde_out, uint64_t *tree_out, const uint64_t 
         if (cb > 128) cb = 128;
         size_t free_b = 0, total_b = 0;
         CU(cudaMemGetInfo(&free_b, &total_b));
-        free_b += g.arena_bytes + g.pool[2].bytes; // ours to reuse: the arena and the cached staging block
+        free_b += g.pool[2].bytes; // ours to reuse: the cached staging block ...
         const size_t per_col = (size_t)(3 * n + n_ext) * 8; // coef + pass scratch + two staging buffers
-        while (cb > 32 && per_col * cb + ((size_t)1 << 30) > free_b) cb -= 32;
+        // ... and the arena, but only as far as this call needs it: an arena left larger by an earlier call is kept, not handed back
+        auto fits = [&](u64 c) { return per_col * c + ((size_t)1 << 30) <= free_b + std::min<size_t>(g.arena_bytes, (size_t)((n + n_ext) * 8 * c)); };
+        while (cb > 32 && !fits(cb)) cb -= 32;
         if (cb > ncols) cb = ncols;
         const u64 cp = pad16(cb);
         TRY(arena_reserve((size_t)(n + n_ext) * cp * 8));
@@ -1802,9 +1805,9 @@ int gl_commit_mgpu_host(uint64_t *row_panels_host, uint64_t *subtree_host, const
         if (cb > 128) cb = 128;
         size_t free_b = 0, total_b = 0;
         CU(cudaMemGetInfo(&free_b, &total_b));
-        free_b += g.arena_bytes;
         const size_t per_col = (size_t)(3 * n + n_ext) * 8; // coef + pass scratch + two staging buffers
-        while (cb > 32 && per_col * cb + ((size_t)1 << 30) > free_b) cb -= 32;
+        auto fits = [&](u64 c) { return per_col * c + ((size_t)1 << 30) <= free_b + std::min<size_t>(g.arena_bytes, (size_t)((n + n_ext) * 8 * c)); };
+        while (cb > 32 && !fits(cb)) cb -= 32;
         if (cb > w) cb = w;
         const u64 cp = pad16(cb);
         TRY(arena_reserve((size_t)(n + n_ext) * cp * 8));
