@@ -311,25 +311,36 @@ int launch_pass_cw(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
     return launch_pass_inst<B2, LAST, CW, false>(p, ntiles, coltiles);
 }
 
-// Full 32-column tiles in one launch; a ragged remainder of <= 16 (<= 8) columns in a second launch that packs two
-// (four) row-tiles into each warp -- only for the wide passes of large transforms, where it matters.
+// Full 32-column tiles in one launch; a ragged remainder of <= 24 columns in one or two more launches that pack two (four)
+// row-tiles into each warp: 16 columns (CW = 16), then what is left as <= 8 (CW = 8) or <= 16 -- a remainder of 17..24 columns used
+// to cost a whole 32-column tile (c2 on 4 GPUs: 152 = 4 x 32 + 24 columns per rank ran as long as 160).  Only for the wide passes of
+// large transforms, where it matters.
 template <int B2, bool LAST>
 int launch_pass_t(const ntt::PassParams &p, u64 ntiles, u32 coltiles)
 {
-    const u32 rag = p.ncols % ntt::kTileCols;
+    u32 rag = p.ncols % ntt::kTileCols;
     const bool big = p.roots_hi || (p.scale_mode == 2 && !p.rscale); // domains above 2^27: full-width tiles only (launch_pass_cw)
-    if (B2 >= 3 && rag != 0 && rag <= 16 && ntiles >= 4 && !big) {
-        const u32 full = p.ncols - rag;
-        if (full) {
+    if (B2 >= 3 && rag != 0 && rag <= 24 && ntiles >= 4 && !big) {
+        u32 done = p.ncols - rag;
+        if (done) {
             ntt::PassParams q = p;
-            q.ncols = full;
+            q.ncols = done;
             TRY((launch_pass_cw<B2, LAST, ntt::kTileCols>(q, ntiles, coltiles - 1)));
         }
+        if (rag > 16) {
+            ntt::PassParams q = p;
+            q.src = p.src + done;
+            q.dst = p.dst + done;
+            q.ncols = 16;
+            TRY((launch_pass_cw<(B2 >= 3 ? B2 : 3), LAST, 16>(q, ntiles, 1)));
+            done += 16;
+            rag -= 16;
+        }
         ntt::PassParams q = p;
-        q.src = p.src + full;
-        q.dst = p.dst + full;
+        q.src = p.src + done;
+        q.dst = p.dst + done;
         q.ncols = rag;
-        if (B2 >= 3 && rag <= 8) return launch_pass_cw<(B2 >= 3 ? B2 : 3), LAST, 8>(q, ntiles, 1);
+        if (rag <= 8) return launch_pass_cw<(B2 >= 3 ? B2 : 3), LAST, 8>(q, ntiles, 1);
         return launch_pass_cw<(B2 >= 3 ? B2 : 3), LAST, 16>(q, ntiles, 1);
     }
     return launch_pass_cw<B2, LAST, ntt::kTileCols>(p, ntiles, coltiles);

@@ -133,6 +133,20 @@ def test_ntt_vs_oracle_all_sizes(glb, oracle, logn):
         assert np.array_equal(glb.ntt_host(f, inverse=True), a % np.uint64(P)), (n, c, "roundtrip")
 
 
+@pytest.mark.parametrize("logn,c", [(10, 17), (10, 24), (14, 55), (16, 88), (15, 20)])
+def test_ntt_ragged_17_to_24_columns(glb, oracle, logn, c):
+    """A ragged last column tile of 17..24 columns runs as a 16-column launch plus a <= 8-column launch (two / four row-tiles per
+    warp) in the passes of >= 7 bits; every word against the oracle, all three transforms and an LDE."""
+    rng = np.random.default_rng(300 + logn + c)
+    n = 1 << logn
+    a = rng.integers(0, 2**64 - 1, size=(n, c), dtype=np.uint64, endpoint=True)
+    assert np.array_equal(glb.ntt_host(a), oracle.ntt(a)), "fwd"
+    assert np.array_equal(glb.ntt_host(a, inverse=True), oracle.ntt(a, inverse=True)), "inv"
+    assert np.array_equal(glb.ntt_host(a, inverse=True, extend=True), oracle.ntt(a, inverse=True, extend=True)), "ext"
+    if logn <= 14:
+        assert np.array_equal(glb.extend_pol_host(a, 4 * n), oracle.extend_pol(a, 4 * n)), "lde"
+
+
 def test_ntt_empty_is_noop(glb):
     a = np.zeros((0, 4), dtype=np.uint64)
     assert glb.ntt_host(a).shape == (0, 4)
