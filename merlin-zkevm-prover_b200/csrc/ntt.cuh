@@ -90,12 +90,13 @@ __device__ __forceinline__ u64 mul_pow2_sel(u64 d, int sh)
 // (Goldilocks::W[1..6] = 2^96, 2^48, 2^24, 2^12, 2^6, 2^3; goldilocks_base_field.cpp:11-18), so a butterfly
 // is canon (4) + add (4) + sub (5) instructions and, for 17 of the 32 butterflies of a radix-16, a
 // 6-8 instruction shift-multiply.  Values stay lazily reduced; only the subtrahend is canonicalised.
-template <int LOG, bool CSEL = false>
+// SBEG > 0: the caller has already done stages 0 .. SBEG-1 (dft16_ztop: trivial stages of a zero-padded input).
+template <int LOG, bool CSEL = false, int SBEG = 0>
 __device__ __forceinline__ void dft_regs(u64 *x)
 {
     constexpr int N = 1 << LOG;
 #pragma unroll
-    for (int s = 0; s < LOG; s++) {
+    for (int s = SBEG; s < LOG; s++) {
         const int half = N >> (s + 1);
 #pragma unroll
         for (int blk = 0; blk < (1 << s); blk++) {
@@ -109,6 +110,23 @@ __device__ __forceinline__ void dft_regs(u64 *x)
             }
         }
     }
+}
+
+// Radix-16 of a column whose registers 8..15 are zero (the first pass of an extended forward transform: rows >= nvalid of the source
+// are padding, and with blowup >= 2 that is the upper half of every thread's 16 rows).  Stage 0 has nothing to add: x[i] stays and
+// x[i + 8] = x[i] * w_16^i -- exactly the words the general butterflies produce from a zero operand (a + 0 and a - 0 return a's bits
+// unchanged), so the results stay bit-identical.  ALL: only register 0 is non-zero (blowup >= 16): the transform of a delta is constant.
+template <bool CSEL, bool ALL>
+__device__ __forceinline__ void dft16_ztop(u64 *x)
+{
+    if (ALL) {
+#pragma unroll
+        for (int i = 1; i < 16; i++) x[i] = x[0];
+        return;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i + 8] = mul_pow2_sel(x[i], 12 * i);
+    dft_regs<4, CSEL, 1>(x);
 }
 
 template <int V> struct IntTag { static constexpr int value = V; };
@@ -217,8 +235,16 @@ __global__ void __launch_bounds__(32 << B2, (B2 >= 4 ? 2 : (B2 == 3 ? 4 : 1))) k
         }
     }
 
-    // ---- step 1: radix-16 over i1 (row = (i1*R2 + t) within the tile)
-    dft_regs<4, kCsel>(x);
+    // ---- step 1: radix-16 over i1 (row = (i1*R2 + t) within the tile).  With a zero-padded source no thread of the grid has more than
+    // ivmax non-zero rows (grid-uniform): the trivial butterflies are skipped
+    if (PAD) {
+        const u64 ivmax = p.nvalid ? ((p.nvalid - 1) >> (p.log_rest + B2)) + 1 : 0;
+        if (ivmax <= 1) dft16_ztop<kCsel, true>(x);
+        else if (ivmax <= 8) dft16_ztop<kCsel, false>(x);
+        else dft_regs<4, kCsel>(x);
+    } else {
+        dft_regs<4, kCsel>(x);
+    }
 
     if (B2 > 0) {
         // ---- twiddle w_R^(t*k1), exchange through shared memory, step 2: radix-R2 over t
