@@ -109,14 +109,15 @@ def run(args, glb, dist, rank, world, local_rank, config, workloads):
     hbm_peak, peak_src = peaks()
     leaf_perm, tree_perm = permutations(loge, ncols)
     leaf_bytes = (e * ncols * 8 + e * 32) / world
-    # mgpu_exchange_and_hash in csrc/glb200.cu: chunks of 1, 3, 9, ... waves of the leaf kernel (148 SMs x 4 CTAs x 128 rows), the last takes the rest
+    # mgpu_exchange_and_hash in csrc/glb200.cu: chunks of 1, 3, 9, ... waves of the leaf kernel (148 SMs x 4 CTAs x 128 rows); the last takes
+    # the rest once that is no more than three times its predecessor
     wave, size, done, chunks = 148 * 4 * 128, 148 * 4 * 128, 0, 0
-    while chunks < 7 and rows > wave * 4 and rows - done > 4 * size:
+    while chunks < 7 and rows > wave * 4 and rows - done > size:
         done, size, chunks = done + size, size * 3, chunks + 1
     chunks += 1
     first_frac = wave / rows if chunks > 1 else 1.0
     config = dict(config)
-    config["parallelism"] = "column-split LDE x%d -> NCCL all-to-all -> row-block leaf hash + subtrees -> gathered root" % world
+    config["parallelism"] = "column-split LDE x%d -> all-to-all over NVLink (copy engines) -> row-block leaf hash + subtrees -> gathered root" % world
     line = {"metric": "commit_ext_elements_per_s", "value": e * ncols / (dev_ms / 1e3), "unit": "ext-elem/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms, "wall_ms_per_step": wall * 1e3 / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "u64 (Goldilocks field, integer pipe)", "data": "synthetic (splitmix64 of the element index mod p, generated in HBM)",
